@@ -1,0 +1,42 @@
+# Build of the native core for sm_100a (B200).  No GPU is needed to build.
+#   make            -> game-of-life---mpi-cuda_b200/_lib/libgol_b200.so + bin/gol
+#   make sass       -> profiles/sass/*.sass listings of the hot kernels
+NVCC      ?= nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS   := $(ARCH) -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function
+PKG       := game-of-life---mpi-cuda_b200
+LIB       := $(PKG)/_lib/libgol_b200.so
+BIN       := bin/gol
+OBJDIR    := build
+CU_SRCS   := csrc/kernels.cu csrc/world.cu csrc/noalloc.cu
+CXX_SRCS  := csrc/cpu_ref.cpp
+CU_SRCS   := $(wildcard $(CU_SRCS))
+OBJS      := $(patsubst csrc/%.cu,$(OBJDIR)/%.o,$(CU_SRCS)) $(patsubst csrc/%.cpp,$(OBJDIR)/%.o,$(CXX_SRCS))
+HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
+
+all: $(LIB) $(BIN)
+
+$(OBJDIR)/%.o: csrc/%.cu $(HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(OBJDIR)/%.o: csrc/%.cpp $(HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+$(LIB): $(OBJS)
+	@mkdir -p $(dir $@)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart_static -ldl -lrt -lpthread
+
+$(BIN): csrc/cli_main.cpp $(LIB) $(HDRS)
+	@mkdir -p bin
+	g++ -O2 -std=c++17 -Wall -o $@ csrc/cli_main.cpp -L$(PKG)/_lib -lgol_b200 -Wl,-rpath,'$$ORIGIN/../$(PKG)/_lib' -lpthread
+
+sass: $(LIB)
+	@mkdir -p profiles/sass
+	cuobjdump -sass $(LIB) > profiles/sass/libgol_b200.sass
+
+clean:
+	rm -rf $(OBJDIR) $(LIB) $(BIN)
+
+.PHONY: all clean sass

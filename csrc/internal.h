@@ -1,0 +1,73 @@
+// internal.h — declarations shared between the translation units of the core.
+#pragma once
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+
+#include "life_math.h"
+
+namespace gol {
+
+int set_error(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3)));
+
+int make_pattern_args(PatternArgs* a, int pattern, int64_t W, int64_t H, int rank, int nranks,
+                      uint64_t seed, double density);
+int write_rank_header(FILE* fp, int rank);
+void append_row_prefix(std::string* s, int64_t global_row);
+
+// Packed CPU step of nrows rows; in_rows has nrows + 2 entries (ghost above /
+// below at the ends), out_rows has nrows.
+void cpu_step_rows(const uint64_t* const* in_rows, uint64_t* const* out_rows, int64_t nrows,
+                   int64_t W);
+
+// ---------------------------------------------------------------------------
+// Device-resident description of one slab (one rank's share of the torus).
+// Lives in device memory; the kernels take a pointer to an array of these, so a
+// captured CUDA graph or a persistent kernel never needs host-side parameter
+// patching: buffer parity, exchange parity and flag targets all come from the
+// counters below, which the kernels themselves advance.
+//
+// Slab buffer: (H + 2*G) rows x stride words, rows [0,G) and [G+H, G+H+2G) are
+// the in-slab margin used when a halo is deeper than one pass (the pass
+// computes part of the neighbour's rows redundantly).  Freshly exchanged halo
+// rows never land in the slab: they land in recv[side][exchange parity], which
+// only the neighbour writes and only this slab reads.
+// ---------------------------------------------------------------------------
+struct SlabState {
+  // geometry
+  int64_t W, H;        // cells per row, interior rows
+  int64_t ws;          // valid words per row
+  int64_t stride;      // row stride in words
+  int32_t G;           // margin rows per side (= GOL_MAX_GHOST capped by plan)
+  int32_t rank, nranks;
+  int32_t pad0;
+  // storage (all device pointers valid on the device that runs this slab)
+  uint64_t* buf[2];              // buf[pass & 1] is the current generation
+  uint64_t* recv[2][2];          // [side 0=top,1=bottom][exchange parity], G x stride each
+  uint64_t* peer_recv[2][2];     // [0]: prev rank's bottom recv, [1]: next rank's top recv
+  unsigned long long* flag[2];       // words received so far on [top, bottom] (monotonic)
+  unsigned long long* peer_flag[2];  // [0]: prev's bottom flag, [1]: next's top flag
+  // counters advanced by the kernels
+  unsigned long long pass;       // passes completed -> buffer parity
+  unsigned long long exch;       // exchanges consumed -> recv parity
+  unsigned long long words_seen; // flag value after the last consumed exchange
+  unsigned int done;             // CTAs finished in the running launch
+  int error;                     // != 0: device-side failure (watchdog)
+  unsigned long long watchdog_ns;
+};
+
+// Baked per launch (identical on every rank: the schedule is SPMD).
+struct PassParams {
+  int32_t ext_in;     // halo rows valid around the interior in the input
+  int32_t k;          // generations this pass (== template K for the fused kernel)
+  int32_t consume;    // 1: input halo comes from recv[] and must be waited for
+  int32_t push;       // rows to push to each neighbour after this pass (0 = none)
+  int32_t strip_rows; // output rows per warp task
+  int32_t col_groups; // warp tasks per strip
+  int32_t nstrips;
+  int32_t pad;
+};
+
+}  // namespace gol

@@ -1,0 +1,829 @@
+// kernels.cu — every device kernel of the core, written for sm_100a.
+//
+// The hot kernel is life_fused<K>: one warp streams a strip of rows top to
+// bottom through K pipelined generation stages held entirely in registers.
+// Each lane owns one 64-cell word column; the two x-neighbour bits a stage
+// needs come from the adjacent lanes by warp shuffle, lanes 0 and 31 are halo
+// lanes whose columns belong to the neighbouring warp task.  There is no shared
+// memory and no block barrier on the hot path: the kernel is bound by the
+// integer (LOP3/SHF) pipes, which is the roofline for bit-sliced Life once the
+// 16384^2 slab is L2-resident.
+//
+// The halo exchange of the reference (MPI_Irecv/Isend/Wait, gol-main.c:97-111)
+// is fused into the same kernel: the warps that produce a slab's first / last
+// rows also store them into the ring neighbour's recv buffer through a peer
+// (NVLink P2P or CUDA-IPC) pointer and publish a word count with
+// red.release.sys; the warps that need a fresh halo spin on ld.acquire.sys.
+// Those warps are scheduled first (lowest task ids).
+#include <cooperative_groups.h>
+
+#include "kernels.cuh"
+
+namespace gol {
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kValidLanes = 30;  // lanes 1..30 own output columns
+
+// ---- system-scope ordering primitives --------------------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Peer / streaming stores: the output of a pass is not re-read by this SM.
+__device__ __forceinline__ void st_cg(uint64_t* p, uint64_t v) { __stcg((unsigned long long*)p, v); }
+__device__ __forceinline__ uint64_t ld_cg(const uint64_t* p) {
+  return __ldcg((const unsigned long long*)p);
+}
+
+// One lane spins until the neighbour has delivered `target` words (monotonic
+// counter).  A dead peer must not hang the GPU: after watchdog_ns the slab is
+// marked failed and the pass continues on whatever is in the buffer.
+__device__ __noinline__ void wait_words(SlabState* st, int side, unsigned long long target) {
+  const unsigned long long* f = st->flag[side];
+  if (ld_acquire_sys(f) >= target) return;
+  const unsigned long long t0 = globaltimer_ns();
+  const unsigned long long limit = st->watchdog_ns;
+  unsigned ns = 20;
+  while (ld_acquire_sys(f) < target) {
+    __nanosleep(ns);
+    if (ns < 640) ns <<= 1;
+    if (globaltimer_ns() - t0 > limit) {
+      atomicExch(&st->error, 1 + side);
+      return;
+    }
+  }
+}
+
+// Everything a pass needs about one slab, resolved from SlabState counters.
+struct PassCtx {
+  const uint64_t* in;     // interior row 0 of the input buffer
+  uint64_t* out;          // interior row 0 of the output buffer
+  const uint64_t* rtop;   // recv top: row 0 <-> y = -ext_in
+  const uint64_t* rbot;   // recv bottom: row 0 <-> y = H
+  uint64_t* ptop;         // prev rank's bottom recv (my rows [0,push))
+  uint64_t* pbot;         // next rank's top recv (my rows [H-push,H))
+  unsigned long long target;
+  int64_t H, ws, stride;
+  int ext_in, consume, push;
+};
+
+__device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long long pass,
+                                            unsigned long long exch, unsigned long long words_seen,
+                                            int ext_in, int consume, int push) {
+  PassCtx c;
+  const int64_t stride = st->stride;
+  c.in = st->buf[pass & 1] + (int64_t)st->G * stride;
+  c.out = st->buf[(pass + 1) & 1] + (int64_t)st->G * stride;
+  c.rtop = st->recv[0][exch & 1];
+  c.rbot = st->recv[1][exch & 1];
+  const unsigned long long pe = exch + (consume ? 1ull : 0ull);
+  c.ptop = st->peer_recv[0][pe & 1];
+  c.pbot = st->peer_recv[1][pe & 1];
+  c.target = words_seen + (unsigned long long)ext_in * (unsigned long long)st->ws;
+  c.H = st->H;
+  c.ws = st->ws;
+  c.stride = stride;
+  c.ext_in = ext_in;
+  c.consume = consume;
+  c.push = push;
+  return c;
+}
+
+// x-neighbour words of `c` inside a warp row: bit j of L is the cell left of
+// bit j of c, the carry bit comes from the lane to the left.
+__device__ __forceinline__ void lane_neighbours(uint64_t c, uint64_t& L, uint64_t& R) {
+  const uint32_t lo = (uint32_t)c, hi = (uint32_t)(c >> 32);
+  const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);
+  const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);
+  const uint32_t Llo = __funnelshift_l(lhi, lo, 1), Lhi = __funnelshift_l(lo, hi, 1);
+  const uint32_t Rlo = __funnelshift_r(lo, hi, 1), Rhi = __funnelshift_r(hi, rlo, 1);
+  L = ((uint64_t)Lhi << 32) | Llo;
+  R = ((uint64_t)Rhi << 32) | Rlo;
+}
+
+struct Stage {
+  HSum<uint64_t> a, b;  // horizontal sums of the two previous rows
+  uint64_t c;           // centre word of the previous row
+};
+
+// Push one row through K generation stages.  Fed rows y_in+0, y_in+1, ... the
+// value returned at step i (i >= 2K) is generation +K of row y_in + i - K.
+template <int K>
+__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x) {
+#pragma unroll
+  for (int t = 0; t < K; ++t) {
+    uint64_t L, R;
+    lane_neighbours(x, L, R);
+    const HSum<uint64_t> h = hsum3(L, x, R);
+    const uint64_t o = life_rule(s[t].a, s[t].b, h, s[t].c);
+    s[t].a = s[t].b;
+    s[t].b = h;
+    s[t].c = x;
+    x = o;
+  }
+  return x;
+}
+
+// One warp task of a fused pass: strip `strip` of column group `cg`.
+template <int K>
+__device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int strip_rows,
+                                           int strip, int cg, int lane) {
+  constexpr int B = 4;  // rows per load batch (software prefetch depth)
+  const int ext_out = c.ext_in - K;
+  const int64_t y_first = -(int64_t)ext_out;
+  const int64_t y_end_all = c.H + ext_out;
+  const int64_t y0 = y_first + (int64_t)strip * strip_rows;
+  int64_t y1 = y0 + strip_rows;
+  if (y1 > y_end_all) y1 = y_end_all;
+
+  // my word column (torus wrap in x, also when the row has < 32 words)
+  int64_t wi = (int64_t)cg * kValidLanes - 1 + lane;
+  wi %= c.ws;
+  if (wi < 0) wi += c.ws;
+  const bool owner = lane >= 1 && lane <= kValidLanes && ((int64_t)cg * kValidLanes + lane - 1) < c.ws;
+
+  const bool reads_top = c.consume && (y0 - K < 0);
+  const bool reads_bot = c.consume && (y1 + K > c.H);
+  if (reads_top || reads_bot) {
+    if (lane == 0) {
+      if (reads_top) wait_words(st, 0, c.target);
+      if (reads_bot) wait_words(st, 1, c.target);
+    }
+    __syncwarp();
+  }
+
+  const int64_t y_in = y0 - K;
+  const int n_in = (int)(y1 - y0) + 2 * K;
+  const uint64_t* in_col = c.in + wi;
+  const uint64_t* top_col = c.rtop + wi + (int64_t)c.ext_in * c.stride;  // row y at top_col + y*stride (y<0)
+  const uint64_t* bot_col = c.rbot + wi - c.H * c.stride;                // row y at bot_col + y*stride (y>=H)
+  const bool fresh = c.consume != 0;
+
+  auto load_row = [&](int64_t y) -> uint64_t {
+    if (fresh && y < 0) return ld_cg(top_col + y * c.stride);
+    if (fresh && y >= c.H) return ld_cg(bot_col + y * c.stride);
+    return in_col[y * c.stride];
+  };
+
+  Stage s[K];
+#pragma unroll
+  for (int t = 0; t < K; ++t) {
+    s[t].a.s0 = s[t].a.s1 = s[t].b.s0 = s[t].b.s1 = s[t].c = 0;
+  }
+
+  uint64_t* out_col = c.out + wi;
+  const int64_t push_lo = c.push;            // rows [0, push) go to prev
+  const int64_t push_hi = c.H - c.push;      // rows [H-push, H) go to next
+  int rows_top = 0, rows_bot = 0;
+
+  uint64_t nxt[B];
+#pragma unroll
+  for (int j = 0; j < B; ++j) nxt[j] = (j < n_in) ? load_row(y_in + j) : 0ull;
+
+  for (int i0 = 0; i0 < n_in; i0 += B) {
+    uint64_t cur[B];
+#pragma unroll
+    for (int j = 0; j < B; ++j) cur[j] = nxt[j];
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const int i = i0 + B + j;
+      nxt[j] = (i < n_in) ? load_row(y_in + i) : 0ull;
+    }
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const int i = i0 + j;
+      if (i < n_in) {
+        const uint64_t o = push_row<K>(s, cur[j]);
+        if (i >= 2 * K) {
+          const int64_t y = y_in + i - K;
+          if (owner) st_cg(out_col + y * c.stride, o);
+          if (c.push) {
+            if (y >= 0 && y < push_lo) {
+              if (owner) st_cg(c.ptop + y * c.stride + wi, o);
+              ++rows_top;
+            }
+            if (y >= push_hi && y < c.H) {
+              if (owner) st_cg(c.pbot + (y - push_hi) * c.stride + wi, o);
+              ++rows_bot;
+            }
+          }
+        }
+      }
+    }
+  }
+
+  if (rows_top | rows_bot) {
+    __threadfence_system();
+    __syncwarp();
+    const unsigned owners = __popc(__ballot_sync(kFull, owner));
+    if (lane == 0) {
+      if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
+      if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
+    }
+  }
+}
+
+// boundary strips first: order 0 -> strip 0, order 1 -> last strip, then the interior
+__device__ __forceinline__ int strip_of_order(int order, int nstrips) {
+  if (order == 0) return 0;
+  if (order == 1) return nstrips - 1;
+  return order - 1;
+}
+
+// Last CTA of a launch advances the slab's counters.
+__device__ __forceinline__ void finish_pass(SlabState* st, const PassParams& p, unsigned nctas) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned prev = atomicAdd(&st->done, 1u);
+    if (prev == nctas - 1) {
+      st->done = 0;
+      st->pass += 1;
+      if (p.consume) {
+        st->exch += 1;
+        st->words_seen += (unsigned long long)p.ext_in * (unsigned long long)st->ws;
+      }
+      __threadfence();
+    }
+  }
+}
+
+template <int K, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* states, PassParams p) {
+  SlabState* st = states + blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int task = blockIdx.x * wpb + (threadIdx.x >> 5);
+  const int ntasks = p.nstrips * p.col_groups;
+  if (task < ntasks) {
+    const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push);
+    const int order = task / p.col_groups;
+    const int cg = task - order * p.col_groups;
+    fused_task<K>(st, c, p.strip_rows, strip_of_order(order, p.nstrips), cg, lane);
+  }
+  finish_pass(st, p, gridDim.x);
+}
+
+// ---- N-K2: generic kernel ----------------------------------------------------
+// One thread per 64-cell word, one generation per pass, any W (masked tail
+// word, bit-level x-wrap) and any H >= 1; blockDim is whatever the CLI asked
+// for (gol-main.c:52).  Same recv/flag protocol with depth 1.
+__global__ void life_generic_kernel(SlabState* states, PassParams p) {
+  SlabState* st = states + blockIdx.y;
+  const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, 1, p.consume, p.push);
+  const int64_t total = c.H * c.ws;
+  const int64_t first = (int64_t)blockIdx.x * blockDim.x;
+  int64_t last = first + blockDim.x - 1;
+  if (last >= total) last = total - 1;
+  if (first < total && p.consume) {
+    const bool top = first < c.ws;
+    const bool bot = last >= (c.H - 1) * c.ws;
+    if (threadIdx.x == 0) {
+      if (top) wait_words(st, 0, c.target);
+      if (bot) wait_words(st, 1, c.target);
+    }
+    if (top || bot) __syncthreads();
+  }
+  const int64_t idx = first + threadIdx.x;
+  int sent_top = 0, sent_bot = 0;
+  if (idx < total) {
+    const int64_t y = idx / c.ws;
+    const int64_t w = idx - y * c.ws;
+    const uint64_t* cur = c.in + y * c.stride;
+    const uint64_t* up = (y == 0 && p.consume) ? c.rtop : cur - c.stride;
+    const uint64_t* down = (y == c.H - 1 && p.consume) ? c.rbot : cur + c.stride;
+    const uint64_t v = step_word(up, cur, down, w, c.ws, st->W);
+    c.out[y * c.stride + w] = v;
+    if (p.push) {
+      if (y == 0) { st_cg(c.ptop + w, v); sent_top = 1; }
+      if (y == c.H - 1) { st_cg(c.pbot + w, v); sent_bot = 1; }
+    }
+  }
+  if (p.push) {
+    if (sent_top | sent_bot) __threadfence_system();
+    const int nt = __syncthreads_count(sent_top);
+    const int nb = __syncthreads_count(sent_bot);
+    if (threadIdx.x == 0) {
+      if (nt) red_release_sys_add(st->peer_flag[0], (unsigned long long)nt);
+      if (nb) red_release_sys_add(st->peer_flag[1], (unsigned long long)nb);
+    }
+  }
+  finish_pass(st, p, gridDim.x);
+}
+
+// ---- N-K5: halo prime ----------------------------------------------------------
+// Replaces init_Ghost_rows (gol-with-cuda.cu:32-53): copies the current first
+// and last `depth` rows into the neighbours' recv buffers and publishes them.
+__global__ void halo_prime_kernel(SlabState* states, int depth) {
+  SlabState* st = states + blockIdx.y;
+  const int64_t ws = st->ws, stride = st->stride, H = st->H;
+  const uint64_t* in = st->buf[st->pass & 1] + (int64_t)st->G * stride;
+  uint64_t* ptop = st->peer_recv[0][st->exch & 1];
+  uint64_t* pbot = st->peer_recv[1][st->exch & 1];
+  const int64_t per_side = (int64_t)depth * ws;
+  int sent_top = 0, sent_bot = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * per_side;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int side = i >= per_side;
+    const int64_t j = side ? i - per_side : i;
+    const int64_t r = j / ws, w = j - r * ws;
+    if (!side) {
+      st_cg(ptop + r * stride + w, in[r * stride + w]);
+      ++sent_top;
+    } else {
+      st_cg(pbot + r * stride + w, in[(H - depth + r) * stride + w]);
+      ++sent_bot;
+    }
+  }
+  if (sent_top | sent_bot) __threadfence_system();
+  __shared__ unsigned long long acc[2];
+  if (threadIdx.x == 0) acc[0] = acc[1] = 0;
+  __syncthreads();
+  if (sent_top) atomicAdd(&acc[0], (unsigned long long)sent_top);
+  if (sent_bot) atomicAdd(&acc[1], (unsigned long long)sent_bot);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (acc[0]) red_release_sys_add(st->peer_flag[0], acc[0]);
+    if (acc[1]) red_release_sys_add(st->peer_flag[1], acc[1]);
+  }
+}
+
+// ---- N-K3: persistent kernel ----------------------------------------------------
+// The whole generation loop of the reference (gol-main.c:94-116) in one
+// cooperative launch: prime, then npasses fused passes separated by a grid
+// barrier.  Halo flags from the ring neighbours are the only cross-GPU
+// synchronisation; the host is not involved until the end.
+__device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int nctas,
+                                             unsigned int& epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    ++epoch;
+    __threadfence();
+    atomicAdd(bar, 1u);
+    const unsigned int want = epoch * nctas;
+    while (ld_acquire_gpu_u32(bar) < want) {
+    }
+  }
+  __syncthreads();
+}
+
+template <int K, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) life_persistent_kernel(SlabState* states,
+                                                                     PersistentParams pp) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const int gwarp = blockIdx.x * wpb + (threadIdx.x >> 5);
+  const int nwarps = gridDim.x * wpb;
+  unsigned int epoch = 0;
+
+  // counters at entry (identical for every slab of the launch by construction,
+  // but read per slab to stay general)
+  // prime: push `depth` edge rows of the current generation
+  {
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
+      SlabState* st = states + sidx;
+      const int64_t ws = st->ws, stride = st->stride, H = st->H;
+      const uint64_t* in = st->buf[st->pass & 1] + (int64_t)st->G * stride;
+      uint64_t* ptop = st->peer_recv[0][st->exch & 1];
+      uint64_t* pbot = st->peer_recv[1][st->exch & 1];
+      const int64_t per_side = (int64_t)pp.depth * ws;
+      int sent_top = 0, sent_bot = 0;
+      for (int64_t i = gtid; i < 2 * per_side; i += gthreads) {
+        const int side = i >= per_side;
+        const int64_t j = side ? i - per_side : i;
+        const int64_t r = j / ws, w = j - r * ws;
+        if (!side) {
+          st_cg(ptop + r * stride + w, in[r * stride + w]);
+          ++sent_top;
+        } else {
+          st_cg(pbot + r * stride + w, in[(H - pp.depth + r) * stride + w]);
+          ++sent_bot;
+        }
+      }
+      if (sent_top | sent_bot) {
+        __threadfence_system();
+        if (sent_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)sent_top);
+        if (sent_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)sent_bot);
+      }
+    }
+  }
+
+  for (int pass = 0; pass < pp.npasses; ++pass) {
+    const int pos = pass % pp.passes_per_exchange;
+    const int ext_in = pp.depth - pos * K;
+    const int ext_out = ext_in - K;
+    const int consume = pos == 0;
+    const int push = (ext_out == 0 && pass + 1 < pp.npasses) ? pp.depth : 0;
+    const int nex = pass / pp.passes_per_exchange;  // exchanges fully consumed before this period
+    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
+      SlabState* st = states + sidx;
+      const unsigned long long pass0 = st->pass, exch0 = st->exch, seen0 = st->words_seen;
+      const unsigned long long exch = exch0 + (unsigned long long)nex + (consume ? 0ull : 1ull);
+      const unsigned long long seen =
+          seen0 + (unsigned long long)nex * (unsigned long long)pp.depth * (unsigned long long)st->ws;
+      const PassCtx c = make_ctx(st, pass0 + pass, exch, seen, ext_in, consume, push);
+      const int64_t rows_total = c.H + 2 * ext_out;
+      const int nstrips = (int)((rows_total + pp.pass.strip_rows - 1) / pp.pass.strip_rows);
+      const int ntasks = nstrips * pp.pass.col_groups;
+      for (int task = gwarp; task < ntasks; task += nwarps) {
+        const int order = task / pp.pass.col_groups;
+        const int cg = task - order * pp.pass.col_groups;
+        fused_task<K>(st, c, pp.pass.strip_rows, strip_of_order(order, nstrips), cg, lane);
+      }
+    }
+    grid_barrier(pp.barrier, gridDim.x, epoch);
+  }
+
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int nex = (pp.npasses + pp.passes_per_exchange - 1) / pp.passes_per_exchange;
+    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
+      SlabState* st = states + sidx;
+      st->pass += (unsigned long long)pp.npasses;
+      st->exch += (unsigned long long)nex;
+      st->words_seen += (unsigned long long)nex * (unsigned long long)pp.depth * (unsigned long long)st->ws;
+    }
+    __threadfence();
+  }
+}
+
+// ---- N-K4: pattern initialisers ------------------------------------------------
+__global__ void pattern_init_kernel(uint64_t* rows, int64_t stride, PatternArgs a) {
+  const int64_t ws = words_per_row(a.W);
+  const int64_t total = a.H * ws;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t y = i / ws, w = i - y * ws;
+    uint64_t v;
+    if (a.pattern == kAllOnes) {
+      v = (w == ws - 1) ? tail_mask(a.W) : ~0ull;
+    } else if (a.pattern == kRandom || a.pattern == kGlider) {
+      v = pattern_word(a, y, w);
+    } else {
+      // sparse patterns: only a handful of words are non-zero
+      const bool maybe = (y == 0 || y == a.H - 1) && (w <= 2 || w == ws - 1);
+      v = maybe ? pattern_word(a, y, w) : 0ull;
+    }
+    rows[y * stride + w] = v;
+  }
+}
+
+// ---- N-K7: pack / unpack ---------------------------------------------------------
+__device__ __forceinline__ uint64_t gather8(uint64_t x) {
+  // 8 bytes (any non-zero = alive) -> 8 bits
+  x = (((x & 0x7f7f7f7f7f7f7f7full) + 0x7f7f7f7f7f7f7f7full) | x) & 0x8080808080808080ull;
+  x >>= 7;
+  return (x * 0x0102040810204080ull) >> 56;
+}
+__device__ __forceinline__ uint64_t spread8(uint64_t b) {
+  // 8 bits -> 8 bytes of 0/1
+  uint64_t x = (b * 0x0101010101010101ull) & 0x8040201008040201ull;
+  return ((x + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
+}
+
+__global__ void pack_kernel(const uint8_t* __restrict__ cells, uint64_t* __restrict__ words,
+                            int64_t W, int64_t H, int64_t stride) {
+  const int64_t ws = words_per_row(W);
+  const int64_t total = H * ws;
+  const bool aligned = (W % 8) == 0 && (((uintptr_t)cells) & 7) == 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t y = i / ws, w = i - y * ws;
+    const uint8_t* src = cells + y * W + w * 64;
+    const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
+    uint64_t v = 0;
+    if (aligned && n == 64) {
+      const uint64_t* s8 = (const uint64_t*)src;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v |= gather8(s8[j]) << (8 * j);
+    } else {
+      for (int j = 0; j < n; ++j) v |= (uint64_t)(src[j] != 0) << j;
+    }
+    words[y * stride + w] = v;
+  }
+}
+
+__global__ void unpack_kernel(const uint64_t* __restrict__ words, uint8_t* __restrict__ cells,
+                              int64_t W, int64_t H, int64_t stride) {
+  const int64_t ws = words_per_row(W);
+  const int64_t total = H * ws;
+  const bool aligned = (W % 8) == 0 && (((uintptr_t)cells) & 7) == 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t y = i / ws, w = i - y * ws;
+    const uint64_t v = words[y * stride + w];
+    uint8_t* dst = cells + y * W + w * 64;
+    const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
+    if (aligned && n == 64) {
+      uint64_t* d8 = (uint64_t*)dst;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d8[j] = spread8((v >> (8 * j)) & 0xffull);
+    } else {
+      for (int j = 0; j < n; ++j) dst[j] = (uint8_t)((v >> j) & 1ull);
+    }
+  }
+}
+
+// ---- population ---------------------------------------------------------------------
+__global__ void __launch_bounds__(kPopThreads) population_partial_kernel(
+    const uint64_t* __restrict__ words, int64_t ws, int64_t stride, int64_t H,
+    unsigned long long* __restrict__ partials) {
+  unsigned long long acc = 0;
+  for (int64_t y = blockIdx.x; y < H; y += gridDim.x) {
+    const uint64_t* row = words + y * stride;
+    for (int64_t w = threadIdx.x; w < ws; w += blockDim.x) acc += (unsigned)__popcll(row[w]);
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(kFull, acc, o);
+  __shared__ unsigned long long wsum[kPopThreads / 32];
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+    for (int i = 0; i < kPopThreads / 32; ++i) t += wsum[i];
+    partials[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(kPopThreads) population_final_kernel(
+    const unsigned long long* __restrict__ partials, int n, unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) acc += partials[i];
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(kFull, acc, o);
+  __shared__ unsigned long long wsum[kPopThreads / 32];
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+    for (int i = 0; i < kPopThreads / 32; ++i) t += wsum[i];
+    *out = t;
+  }
+}
+
+// ---- N-K6: row text formatter ----------------------------------------------------------
+// Layout of one output row (gol-main.c:17-28): "Row %2d: " then "%u " per cell
+// then '\n'.  The cell text starts at a 16-byte aligned offset so a word of 64
+// cells becomes eight 16-byte stores; the prefix is written right-aligned in
+// front of it and the host knows its length.
+__global__ void format_rows_kernel(const uint64_t* __restrict__ rows, int64_t stride, int64_t W,
+                                   int64_t nrows, int64_t first_global_row, char* __restrict__ text,
+                                   int64_t pitch) {
+  const int64_t ws = words_per_row(W);
+  const int64_t total = nrows * ws;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / ws, w = i - r * ws;
+    const uint64_t v = rows[r * stride + w];
+    char* row_text = text + r * pitch;
+    char* dst = row_text + kTextCellOff + w * 128;
+    const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
+    if (n == 64) {
+      uint4* d16 = (uint4*)dst;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t b = (uint32_t)(v >> (8 * j)) & 0xffu;
+        uint4 q;
+        q.x = 0x20302030u + (b & 1u) + (((b >> 1) & 1u) << 16);
+        q.y = 0x20302030u + ((b >> 2) & 1u) + (((b >> 3) & 1u) << 16);
+        q.z = 0x20302030u + ((b >> 4) & 1u) + (((b >> 5) & 1u) << 16);
+        q.w = 0x20302030u + ((b >> 6) & 1u) + (((b >> 7) & 1u) << 16);
+        d16[j] = q;
+      }
+    } else {
+      for (int j = 0; j < n; ++j) {
+        dst[2 * j] = (char)('0' + ((v >> j) & 1ull));
+        dst[2 * j + 1] = ' ';
+      }
+    }
+    if (w == ws - 1) row_text[kTextCellOff + 2 * W] = '\n';
+    if (w == 0) {
+      // "Row %2d: " right-aligned so that it ends at kTextCellOff
+      int g = (int)(first_global_row + r);
+      char* p = row_text + kTextCellOff;
+      *--p = ' ';
+      *--p = ':';
+      int digits = 0;
+      const bool neg = g < 0;
+      unsigned u = neg ? 0u - (unsigned)g : (unsigned)g;
+      do {
+        *--p = (char)('0' + u % 10u);
+        u /= 10u;
+        ++digits;
+      } while (u);
+      if (neg) { *--p = '-'; ++digits; }
+      while (digits < 2) { *--p = ' '; ++digits; }
+      *--p = ' ';
+      *--p = 'w';
+      *--p = 'o';
+      *--p = 'R';
+    }
+  }
+}
+
+// ---- stand-alone steps (no ring state) -----------------------------------------------------
+// top / bottom are the rows above row 0 and below row H-1: the slab's own last /
+// first row for a torus, or explicit ghost rows for the unfused NCCL baseline.
+__global__ void step_rows_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+                                 const uint64_t* __restrict__ top, const uint64_t* __restrict__ bottom,
+                                 int64_t W, int64_t H, int64_t stride) {
+  const int64_t ws = words_per_row(W);
+  const int64_t total = H * ws;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t y = i / ws, w = i - y * ws;
+    const uint64_t* cur = in + y * stride;
+    const uint64_t* up = (y == 0) ? top : cur - stride;
+    const uint64_t* down = (y == H - 1) ? bottom : cur + stride;
+    out[y * stride + w] = step_word(up, cur, down, w, ws, W);
+  }
+}
+
+// ---- instantiation table of the K-templated kernels -----------------------------------
+// K      : generations per pass
+// MAXT   : largest block the instantiation accepts (register budget)
+template <int K> struct FusedCfg;
+template <> struct FusedCfg<1> { static constexpr int kMaxT = 256, kMinB = 2; };
+template <> struct FusedCfg<2> { static constexpr int kMaxT = 256, kMinB = 2; };
+template <> struct FusedCfg<3> { static constexpr int kMaxT = 256, kMinB = 2; };
+template <> struct FusedCfg<4> { static constexpr int kMaxT = 256, kMinB = 2; };
+template <> struct FusedCfg<6> { static constexpr int kMaxT = 128, kMinB = 3; };
+template <> struct FusedCfg<8> { static constexpr int kMaxT = 128, kMinB = 3; };
+
+template <int K> const void* fused_fn() {
+  return (const void*)&life_fused_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
+}
+template <int K> const void* persistent_fn() {
+  return (const void*)&life_persistent_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
+}
+
+#define GOL_DISPATCH_K(K, expr)                       \
+  switch (K) {                                        \
+    case 1: { constexpr int KK = 1; expr; } break;    \
+    case 2: { constexpr int KK = 2; expr; } break;    \
+    case 3: { constexpr int KK = 3; expr; } break;    \
+    case 4: { constexpr int KK = 4; expr; } break;    \
+    case 6: { constexpr int KK = 6; expr; } break;    \
+    case 8: { constexpr int KK = 8; expr; } break;    \
+    default: break;                                   \
+  }
+
+}  // namespace
+
+// ---- host side ---------------------------------------------------------------------------
+
+static uint64_t g_launches = 0;
+void count_launch(uint64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }
+uint64_t launch_count_value() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
+bool fused_k_supported(int K) { return K == 1 || K == 2 || K == 3 || K == 4 || K == 6 || K == 8; }
+
+FusedLimits fused_limits(int K) {
+  FusedLimits l{0};
+  GOL_DISPATCH_K(K, l.max_threads = FusedCfg<KK>::kMaxT);
+  return l;
+}
+
+int fused_resident_warps_per_sm(int K, int threads, int device) {
+  (void)device;
+  const void* fn = nullptr;
+  GOL_DISPATCH_K(K, fn = fused_fn<KK>());
+  if (!fn) return 0;
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, threads, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return nb * (threads / 32);
+}
+
+int persistent_max_ctas(int K, int threads, int device) {
+  const void* fn = nullptr;
+  GOL_DISPATCH_K(K, fn = persistent_fn<KK>());
+  if (!fn) return 0;
+  int nb = 0, sms = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, threads, 0) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  return nb * sms;
+}
+
+cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParams& p, int threads,
+                         cudaStream_t s) {
+  const void* fn = nullptr;
+  GOL_DISPATCH_K(K, fn = fused_fn<KK>());
+  if (!fn) return cudaErrorInvalidValue;
+  const int wpb = threads / 32;
+  const int ntasks = p.nstrips * p.col_groups;
+  dim3 grid((unsigned)((ntasks + wpb - 1) / wpb), (unsigned)nslabs);
+  PassParams pp = p;
+  void* args[] = {(void*)&d_states, (void*)&pp};
+  count_launch(1);
+  return cudaLaunchKernel(fn, grid, dim3((unsigned)threads), args, 0, s);
+}
+
+cudaError_t launch_generic(SlabState* d_states, int nslabs, const PassParams& p, int threads,
+                           int64_t max_words, cudaStream_t s) {
+  dim3 grid((unsigned)((max_words + threads - 1) / threads), (unsigned)nslabs);
+  count_launch(1);
+  life_generic_kernel<<<grid, threads, 0, s>>>(d_states, p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max_ws,
+                         cudaStream_t s) {
+  const int threads = 256;
+  int64_t work = 2 * (int64_t)depth * max_ws;
+  int blocks = (int)((work + threads - 1) / threads);
+  if (blocks < 1) blocks = 1;
+  if (blocks > 64) blocks = 64;
+  count_launch(1);
+  halo_prime_kernel<<<dim3((unsigned)blocks, (unsigned)nslabs), threads, 0, s>>>(d_states, depth);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_persistent(int K, SlabState* d_states, const PersistentParams& pp, int threads,
+                              int nctas, cudaStream_t s) {
+  const void* fn = nullptr;
+  GOL_DISPATCH_K(K, fn = persistent_fn<KK>());
+  if (!fn) return cudaErrorInvalidValue;
+  PersistentParams p = pp;
+  void* args[] = {(void*)&d_states, (void*)&p};
+  count_launch(1);
+  return cudaLaunchCooperativeKernel(fn, dim3((unsigned)nctas), dim3((unsigned)threads), args, 0, s);
+}
+
+static int grid_for(int64_t total, int threads) {
+  int64_t b = (total + threads - 1) / threads;
+  if (b < 1) b = 1;
+  if (b > 148 * 32) b = 148 * 32;
+  return (int)b;
+}
+
+cudaError_t launch_pattern_init(uint64_t* d_rows, int64_t stride, const PatternArgs& a,
+                                cudaStream_t s) {
+  const int64_t total = a.H * words_per_row(a.W);
+  count_launch(1);
+  pattern_init_kernel<<<grid_for(total, 256), 256, 0, s>>>(d_rows, stride, a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H,
+                        int64_t stride, cudaStream_t s) {
+  count_launch(1);
+  pack_kernel<<<grid_for(H * words_per_row(W), 256), 256, 0, s>>>(d_cells, d_words, W, H, stride);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H,
+                          int64_t stride, cudaStream_t s) {
+  count_launch(1);
+  unpack_kernel<<<grid_for(H * words_per_row(W), 256), 256, 0, s>>>(d_words, d_cells, W, H, stride);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_population(const uint64_t* d_words, int64_t ws, int64_t stride, int64_t H,
+                              unsigned long long* d_partials, unsigned long long* d_out,
+                              cudaStream_t s) {
+  count_launch(2);
+  population_partial_kernel<<<kPopBlocks, kPopThreads, 0, s>>>(d_words, ws, stride, H, d_partials);
+  population_final_kernel<<<1, kPopThreads, 0, s>>>(d_partials, kPopBlocks, d_out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_format_rows(const uint64_t* d_rows, int64_t stride, int64_t W, int64_t nrows,
+                               int64_t first_global_row, char* d_text, int64_t pitch,
+                               cudaStream_t s) {
+  count_launch(1);
+  format_rows_kernel<<<grid_for(nrows * words_per_row(W), 256), 256, 0, s>>>(
+      d_rows, stride, W, nrows, first_global_row, d_text, pitch);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_top,
+                             const uint64_t* d_bottom, int64_t W, int64_t H, int64_t stride,
+                             int threads, cudaStream_t s) {
+  count_launch(1);
+  step_rows_kernel<<<grid_for(H * words_per_row(W), threads), threads, 0, s>>>(d_in, d_out, d_top, d_bottom,
+                                                                               W, H, stride);
+  return cudaGetLastError();
+}
+
+}  // namespace gol

@@ -1,0 +1,73 @@
+// kernels.cuh — host-callable launch wrappers of every device kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "internal.h"
+
+namespace gol {
+
+// Kernel inventory ("new-framework kernel list"):
+//   life_fused<K>      N-K1  register-streaming K-generation pass + P2P halo push + flags
+//   life_generic       N-K2  one thread per word, any shape, 1 generation, same protocol
+//   life_persistent<K> N-K3  whole step() in one cooperative launch (grid barrier between passes)
+//   pattern_init       N-K4  patterns 0..6 straight into packed words
+//   halo_prime         N-K5  push my edge rows into the neighbours' recv buffers
+//   format_rows        N-K6  bits -> "0 1 0 ..." text rows on the device
+//   pack / unpack      N-K7  byte cells <-> packed words
+//   population         (new) popcount reduction
+
+struct FusedLimits {
+  int max_threads;   // __launch_bounds__ of the instantiation
+};
+FusedLimits fused_limits(int K);
+bool fused_k_supported(int K);
+
+// Resident warps per SM for the fused kernel at a block size (occupancy query).
+int fused_resident_warps_per_sm(int K, int threads, int device);
+int persistent_max_ctas(int K, int threads, int device);
+
+cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParams& p, int threads,
+                         cudaStream_t s);
+cudaError_t launch_generic(SlabState* d_states, int nslabs, const PassParams& p, int threads,
+                           int64_t max_words, cudaStream_t s);
+cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max_ws, cudaStream_t s);
+
+// Persistent: `npasses` identical passes (K gens each, exchange every
+// `passes_per_exchange` passes of depth K * passes_per_exchange).
+struct PersistentParams {
+  PassParams pass;           // strip_rows / col_groups / nstrips for ext_out = 0 are recomputed on device
+  int32_t npasses;
+  int32_t passes_per_exchange;
+  int32_t depth;             // exchange depth = K * passes_per_exchange
+  int32_t nslabs;
+  unsigned int* barrier;     // 2 x u32 in device memory, zero before first use
+};
+cudaError_t launch_persistent(int K, SlabState* d_states, const PersistentParams& pp, int threads,
+                              int nctas, cudaStream_t s);
+
+cudaError_t launch_pattern_init(uint64_t* d_rows, int64_t stride, const PatternArgs& a,
+                                cudaStream_t s);
+cudaError_t launch_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H,
+                        int64_t stride, cudaStream_t s);
+cudaError_t launch_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H,
+                          int64_t stride, cudaStream_t s);
+constexpr int kPopBlocks = 1184;  // 8 x 148
+constexpr int kPopThreads = 256;
+cudaError_t launch_population(const uint64_t* d_words, int64_t ws, int64_t stride, int64_t H,
+                              unsigned long long* d_partials /* kPopBlocks */,
+                              unsigned long long* d_out, cudaStream_t s);
+// Text rows: row r of the chunk starts at d_text + r * pitch; cells begin at
+// byte `cell_off` (16-byte aligned), the prefix "Row %2d: " ends right before it.
+constexpr int kTextCellOff = 32;
+cudaError_t launch_format_rows(const uint64_t* d_rows, int64_t stride, int64_t W, int64_t nrows,
+                               int64_t first_global_row, char* d_text, int64_t pitch,
+                               cudaStream_t s);
+cudaError_t launch_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_top,
+                             const uint64_t* d_bottom, int64_t W, int64_t H, int64_t stride,
+                             int threads, cudaStream_t s);
+
+void count_launch(uint64_t n);
+uint64_t launch_count_value();
+
+}  // namespace gol

@@ -1,0 +1,1099 @@
+// world.cu — the slab/ring runtime behind gol_world_*.
+//
+// Replaces the reference's global-variable "API" (gol-main.c:11-13) and its
+// host-side launch wrapper (gol-with-cuda.cu:264-284) with an explicit world
+// object: per-rank slabs (double-buffered, bit-packed), recv buffers and flags
+// the ring neighbours write into directly, a pass schedule that is identical
+// on every rank, CUDA graphs for the launch-bound inner loop, and device-timed
+// stepping.  A CPU backend shares the ring/ghost logic so that rank routing
+// (R = 1, 2, >= 3) is testable without a GPU.
+#include <cuda_runtime.h>
+#include <errno.h>
+#include <string.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../include/gol_b200.h"
+#include "internal.h"
+#include "kernels.cuh"
+
+namespace gol {
+namespace {
+
+#define CU_TRY(expr)                                                                     \
+  do {                                                                                   \
+    cudaError_t e__ = (expr);                                                            \
+    if (e__ != cudaSuccess)                                                              \
+      return set_error(GOL_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                       __FILE__, __LINE__);                                              \
+  } while (0)
+
+constexpr uint32_t kBlobMagic = 0x474F4C42u;  // "GOLB"
+
+struct ExportBlob {
+  uint32_t magic;
+  int32_t rank, device, pid;
+  int64_t W, H, stride;
+  int32_t G, pad;
+  uint64_t off_flags;
+  uint64_t off_recv[2][2];
+  uint64_t base_addr;
+  cudaIpcMemHandle_t handle;
+};
+static_assert(sizeof(ExportBlob) <= GOL_EXPORT_BYTES, "export blob too large");
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Slab {
+  int rank = 0, device = 0, group = 0, index_in_group = 0;
+  char* base = nullptr;
+  size_t bytes = 0;
+  size_t off_flags = 0, off_recv[2][2] = {{0, 0}, {0, 0}}, off_buf[2] = {0, 0};
+  SlabState h{};
+  unsigned long long* d_partials = nullptr;
+  unsigned long long* d_pop = nullptr;
+  // CPU backend
+  std::vector<uint64_t> cbuf[2];
+  std::vector<uint64_t> cghost[2];
+  int ccur = 0;
+};
+
+struct PassItem {
+  bool prime = false;
+  bool generic = false;
+  int K = 0;
+  int depth = 0;  // prime depth
+  PassParams p{};
+};
+
+struct Group {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::vector<int> slabs;
+  SlabState* d_states = nullptr;
+  unsigned int* d_barrier = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  std::map<int64_t, std::pair<cudaGraphExec_t, int>> graphs;  // gens -> (exec, kernels)
+};
+
+struct Peer {
+  bool imported = false;
+  ExportBlob blob{};
+  char* mapped = nullptr;
+  bool ipc_opened = false;
+  int opened_on = -1;
+};
+
+}  // namespace
+}  // namespace gol
+
+using namespace gol;
+
+struct gol_world {
+  gol_config_t cfg{};
+  gol_plan_t plan{};
+  int64_t W = 0, H = 0, ws = 0, stride = 0;
+  int G = 0;
+  bool cuda = false;
+  bool connected = false;
+  std::vector<Slab> slabs;
+  std::vector<Group> groups;
+  std::vector<Peer> peers;
+  uint64_t pass_host = 0;  // passes enqueued so far (buffer parity of every slab)
+  int resident_warps = 0, sms = 148;
+};
+
+namespace gol {
+namespace {
+
+int pick_strip_rows(int64_t rows_total, int col_groups, int K, int slots) {
+  // one warp task = strip_rows output rows of one column group; cost per task
+  // ~ strip_rows + 2K (pipeline fill) + fixed overhead; the grid runs in waves
+  // of `slots` resident warps.
+  if (slots < 1) slots = 1;
+  int best = 0;
+  double best_cost = 1e300;
+  const int lo = std::max(K, 4);
+  const int hi = (int)std::min<int64_t>(rows_total, 1024);
+  for (int rh = lo; rh <= std::max(lo, hi); ++rh) {
+    const int64_t strips = (rows_total + rh - 1) / rh;
+    const int64_t tasks = strips * col_groups;
+    const int64_t waves = (tasks + slots - 1) / slots;
+    const double cost = (double)waves * ((double)rh + 2.0 * K + 6.0);
+    if (cost < best_cost - 1e-9) {
+      best_cost = cost;
+      best = rh;
+    }
+  }
+  return best > 0 ? best : lo;
+}
+
+int largest_k_le(int limit) {
+  static const int ks[] = {8, 6, 4, 3, 2, 1};
+  for (int k : ks)
+    if (k <= limit) return k;
+  return 1;
+}
+
+int make_plan(gol_world* w) {
+  const gol_config_t& c = w->cfg;
+  gol_plan_t& p = w->plan;
+  memset(&p, 0, sizeof p);
+  p.words_per_row = w->ws;
+  p.row_stride = w->stride;
+  int mode = c.mode;
+  if (mode < GOL_MODE_AUTO || mode > GOL_MODE_TMA)
+    return set_error(GOL_ERR_ARG, "unknown mode %d", mode);
+  int K = c.temporal_k > 0 ? c.temporal_k : 4;
+  int depth = c.exchange_depth > 0 ? c.exchange_depth : K;
+  const bool shape_ok = (w->W % 64) == 0;
+  if (!w->cuda) {
+    p.mode = GOL_MODE_GENERIC;
+    p.temporal_k = 1;
+    p.exchange_depth = 1;
+    p.threads_per_block = c.threads_per_block;
+    p.slab_rows = w->H;
+    return GOL_OK;
+  }
+  if (mode == GOL_MODE_AUTO) {
+    if (shape_ok) {
+      while (depth > w->H && depth > 1) depth /= 2;
+      if (K > depth) K = largest_k_le(depth);
+      mode = GOL_MODE_FUSED;
+    } else {
+      mode = GOL_MODE_GENERIC;
+    }
+  }
+  if (mode == GOL_MODE_TMA) mode = GOL_MODE_FUSED;  // TMA-fed variant selects itself inside the fused path
+  if (mode == GOL_MODE_GENERIC) {
+    int t = c.threads_per_block > 0 ? c.threads_per_block : 256;
+    if (t < 1 || t > 1024)
+      return set_error(GOL_ERR_ARG, "threads per block must be in [1,1024], got %d", t);
+    p.mode = mode;
+    p.temporal_k = 1;
+    p.exchange_depth = 1;
+    p.threads_per_block = t;
+    p.slab_rows = w->H + 2 * w->G;
+    return GOL_OK;
+  }
+  // fused / persistent
+  if (!shape_ok)
+    return set_error(GOL_ERR_UNSUPPORTED,
+                     "fused kernels need a width that is a multiple of 64 (got %lld); use mode generic",
+                     (long long)w->W);
+  if (!fused_k_supported(K))
+    return set_error(GOL_ERR_ARG, "temporal_k must be one of 1,2,3,4,6,8 (got %d)", K);
+  if (depth % K != 0 || depth > GOL_MAX_GHOST || depth < K)
+    return set_error(GOL_ERR_ARG, "exchange_depth must be a multiple of temporal_k and <= %d (got %d, k=%d)",
+                     GOL_MAX_GHOST, depth, K);
+  if (depth > w->H)
+    return set_error(GOL_ERR_ARG, "exchange_depth %d exceeds the slab height %lld", depth, (long long)w->H);
+  int t = c.threads_per_block > 0 ? c.threads_per_block : 128;
+  if (t < 1 || t > 1024)
+    return set_error(GOL_ERR_ARG, "threads per block must be in [1,1024], got %d", t);
+  t = std::max(32, (t / 32) * 32);  // whole warps
+  const int lim = fused_limits(K).max_threads;
+  if (t > lim) t = lim;             // register budget of the K-generation pipeline
+  p.mode = mode;
+  p.temporal_k = K;
+  p.exchange_depth = depth;
+  p.threads_per_block = t;
+  p.col_groups = (int)((w->ws + 29) / 30);
+  p.slab_rows = w->H + 2 * w->G;
+  return GOL_OK;
+}
+
+int finish_plan_cuda(gol_world* w) {
+  gol_plan_t& p = w->plan;
+  if (p.mode != GOL_MODE_FUSED && p.mode != GOL_MODE_PERSISTENT) return GOL_OK;
+  const int dev = w->groups.empty() ? 0 : w->groups[0].device;
+  CU_TRY(cudaSetDevice(dev));
+  CU_TRY(cudaDeviceGetAttribute(&w->sms, cudaDevAttrMultiProcessorCount, dev));
+  int rw = fused_resident_warps_per_sm(p.temporal_k, p.threads_per_block, dev);
+  if (rw < 1) rw = 8;
+  w->resident_warps = rw;
+  const int slabs_per_dev = (int)w->groups[0].slabs.size();
+  int slots = w->sms * rw / std::max(1, slabs_per_dev);
+  if (p.mode == GOL_MODE_PERSISTENT) {
+    const int wpb = p.threads_per_block / 32;
+    const int ctas = persistent_max_ctas(p.temporal_k, p.threads_per_block, dev);
+    if (ctas > 0) slots = ctas * wpb / std::max(1, slabs_per_dev);
+  }
+  p.strip_rows = pick_strip_rows(w->H, p.col_groups, p.temporal_k, slots);
+  const int wpb = p.threads_per_block / 32;
+  const int64_t strips = (w->H + p.strip_rows - 1) / p.strip_rows;
+  p.ctas_per_slab = (int)((strips * p.col_groups + wpb - 1) / wpb);
+  p.regs_hint = rw;
+  return GOL_OK;
+}
+
+void fill_strips(const gol_world* w, PassParams* pp) {
+  const int ext_out = pp->ext_in - pp->k;
+  const int64_t rows_total = w->H + 2 * ext_out;
+  pp->strip_rows = w->plan.strip_rows;
+  pp->col_groups = w->plan.col_groups;
+  pp->nstrips = (int)((rows_total + pp->strip_rows - 1) / pp->strip_rows);
+}
+
+// The pass schedule for `gens` generations; identical on every rank.
+std::vector<PassItem> build_schedule(const gol_world* w, int64_t gens) {
+  std::vector<PassItem> items;
+  if (gens <= 0) return items;
+  const gol_plan_t& pl = w->plan;
+  if (pl.mode == GOL_MODE_GENERIC) {
+    PassItem pr;
+    pr.prime = true;
+    pr.depth = 1;
+    items.push_back(pr);
+    for (int64_t g = 0; g < gens; ++g) {
+      PassItem it;
+      it.generic = true;
+      it.K = 1;
+      it.p.ext_in = 1;
+      it.p.k = 1;
+      it.p.consume = 1;
+      it.p.push = (g + 1 < gens) ? 1 : 0;
+      items.push_back(it);
+    }
+    return items;
+  }
+  int64_t remaining = gens;
+  bool first = true;
+  while (remaining > 0) {
+    const int d = (int)std::min<int64_t>(pl.exchange_depth, remaining);
+    if (first) {
+      PassItem pr;
+      pr.prime = true;
+      pr.depth = d;
+      items.push_back(pr);
+      first = false;
+    }
+    int ext = d;
+    while (ext > 0) {
+      const int k = largest_k_le(std::min(pl.temporal_k, ext));
+      PassItem it;
+      it.K = k;
+      it.p.ext_in = ext;
+      it.p.k = k;
+      it.p.consume = (ext == d) ? 1 : 0;
+      it.p.push = 0;
+      ext -= k;
+      if (ext == 0) {
+        const int64_t left = remaining - d;
+        it.p.push = left > 0 ? (int)std::min<int64_t>(pl.exchange_depth, left) : 0;
+      }
+      fill_strips(w, &it.p);
+      items.push_back(it);
+    }
+    remaining -= d;
+  }
+  return items;
+}
+
+int launch_item(gol_world* w, Group& g, const PassItem& it) {
+  const int n = (int)g.slabs.size();
+  cudaError_t e;
+  if (it.prime) {
+    e = launch_prime(g.d_states, n, it.depth, w->ws, g.stream);
+  } else if (it.generic) {
+    e = launch_generic(g.d_states, n, it.p, w->plan.threads_per_block, w->H * w->ws, g.stream);
+  } else {
+    e = launch_fused(it.K, g.d_states, n, it.p, w->plan.threads_per_block, g.stream);
+  }
+  if (e != cudaSuccess)
+    return set_error(GOL_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+  return GOL_OK;
+}
+
+int count_passes(const std::vector<PassItem>& items) {
+  int n = 0;
+  for (auto& it : items) n += it.prime ? 0 : 1;
+  return n;
+}
+
+int upload_states(gol_world* w) {
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    std::vector<SlabState> hs;
+    for (int si : g.slabs) hs.push_back(w->slabs[(size_t)si].h);
+    CU_TRY(cudaMemcpy(g.d_states, hs.data(), hs.size() * sizeof(SlabState), cudaMemcpyHostToDevice));
+  }
+  return GOL_OK;
+}
+
+uint64_t* cur_interior(gol_world* w, Slab& s) {
+  return s.h.buf[w->pass_host & 1] + (int64_t)w->G * w->stride;
+}
+
+int check_local(gol_world* w, int li) {
+  if (!w) return set_error(GOL_ERR_ARG, "null world");
+  if (li < 0 || li >= (int)w->slabs.size())
+    return set_error(GOL_ERR_ARG, "local index %d out of range (nlocal=%d)", li, (int)w->slabs.size());
+  return GOL_OK;
+}
+
+// ---- CPU backend ------------------------------------------------------------
+void cpu_exchange_local(gol_world* w) {
+  // every rank local: ghost above rank r = last row of rank r-1; below = first row of r+1
+  const int R = w->cfg.nranks;
+  for (auto& s : w->slabs) {
+    const Slab& prev = w->slabs[(size_t)((s.rank - 1 + R) % R)];
+    const Slab& next = w->slabs[(size_t)((s.rank + 1) % R)];
+    const uint64_t* pl = prev.cbuf[prev.ccur].data() + (w->H - 1) * w->stride;
+    const uint64_t* nf = next.cbuf[next.ccur].data();
+    std::copy(pl, pl + w->stride, s.cghost[0].begin());
+    std::copy(nf, nf + w->stride, s.cghost[1].begin());
+  }
+}
+
+void cpu_step_slab(gol_world* w, Slab& s) {
+  const int64_t H = w->H, st = w->stride;
+  std::vector<const uint64_t*> in_rows((size_t)H + 2);
+  std::vector<uint64_t*> out_rows((size_t)H);
+  const uint64_t* cur = s.cbuf[s.ccur].data();
+  uint64_t* nxt = s.cbuf[s.ccur ^ 1].data();
+  in_rows[0] = s.cghost[0].data();
+  for (int64_t y = 0; y < H; ++y) in_rows[(size_t)y + 1] = cur + y * st;
+  in_rows[(size_t)H + 1] = s.cghost[1].data();
+  for (int64_t y = 0; y < H; ++y) out_rows[(size_t)y] = nxt + y * st;
+  cpu_step_rows(in_rows.data(), out_rows.data(), H, w->W);
+  s.ccur ^= 1;
+}
+
+}  // namespace
+}  // namespace gol
+
+extern "C" {
+
+uint64_t gol_launch_count(void) { return launch_count_value(); }
+
+gol_world_t* gol_world_create(const gol_config_t* cfg) {
+  if (!cfg) {
+    set_error(GOL_ERR_ARG, "null config");
+    return nullptr;
+  }
+  if (cfg->width < 1 || cfg->rows < 1 || cfg->nranks < 1 || cfg->nlocal < 1 || cfg->first_rank < 0 ||
+      cfg->first_rank + cfg->nlocal > cfg->nranks) {
+    set_error(GOL_ERR_ARG, "bad geometry: width=%lld rows=%lld nranks=%d first=%d nlocal=%d",
+              (long long)cfg->width, (long long)cfg->rows, cfg->nranks, cfg->first_rank, cfg->nlocal);
+    return nullptr;
+  }
+  gol_world* w = new gol_world();
+  w->cfg = *cfg;
+  w->W = cfg->width;
+  w->H = cfg->rows;
+  w->ws = words_per_row(w->W);
+  w->stride = row_stride_words(w->W);
+  w->cuda = cfg->backend == GOL_BACKEND_CUDA;
+  w->G = (int)std::min<int64_t>(GOL_MAX_GHOST, w->H);
+  w->peers.resize((size_t)cfg->nranks);
+  if (make_plan(w) != GOL_OK) {
+    delete w;
+    return nullptr;
+  }
+  w->slabs.resize((size_t)cfg->nlocal);
+  for (int i = 0; i < cfg->nlocal; ++i) w->slabs[(size_t)i].rank = cfg->first_rank + i;
+
+  if (!w->cuda) {
+    for (auto& s : w->slabs) {
+      for (int b = 0; b < 2; ++b) s.cbuf[b].assign((size_t)(w->H * w->stride), 0);
+      for (int b = 0; b < 2; ++b) s.cghost[b].assign((size_t)w->stride, 0);
+    }
+    w->connected = (cfg->nlocal == cfg->nranks);
+    return w;
+  }
+
+  // ---- CUDA: devices, groups, allocations
+  auto fail = [&](void) -> gol_world_t* {
+    gol_world_destroy(w);
+    return nullptr;
+  };
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1) {
+    set_error(GOL_ERR_CUDA, "no CUDA device available: %s", cudaGetErrorString(e));
+    return fail();
+  }
+  int use = cfg->ndevices > 0 ? std::min(cfg->ndevices, ndev) : ndev;
+  for (int i = 0; i < cfg->nlocal; ++i) {
+    Slab& s = w->slabs[(size_t)i];
+    s.device = (cfg->device_base + i) % use;  // rank -> device like gol-with-cuda.cu:296
+    int gi = -1;
+    for (size_t k = 0; k < w->groups.size(); ++k)
+      if (w->groups[k].device == s.device) gi = (int)k;
+    if (gi < 0) {
+      Group g;
+      g.device = s.device;
+      w->groups.push_back(g);
+      gi = (int)w->groups.size() - 1;
+    }
+    s.group = gi;
+    s.index_in_group = (int)w->groups[(size_t)gi].slabs.size();
+    w->groups[(size_t)gi].slabs.push_back(i);
+  }
+  const size_t row_bytes = (size_t)w->stride * 8;
+  const size_t recv_bytes = align_up((size_t)w->G * row_bytes, 256);
+  const size_t buf_bytes = align_up((size_t)(w->H + 2 * w->G) * row_bytes, 256);
+  for (auto& s : w->slabs) {
+    if (cudaSetDevice(s.device) != cudaSuccess) {
+      set_error(GOL_ERR_CUDA, "cudaSetDevice(%d) failed", s.device);
+      return fail();
+    }
+    size_t off = 0;
+    s.off_flags = off;
+    off += 256;
+    for (int side = 0; side < 2; ++side)
+      for (int p = 0; p < 2; ++p) {
+        s.off_recv[side][p] = off;
+        off += recv_bytes;
+      }
+    for (int b = 0; b < 2; ++b) {
+      s.off_buf[b] = off;
+      off += buf_bytes;
+    }
+    s.bytes = off;
+    e = cudaMalloc((void**)&s.base, s.bytes);
+    if (e == cudaSuccess) e = cudaMemset(s.base, 0, s.bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&s.d_partials, (kPopBlocks + 1) * sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+      set_error(GOL_ERR_CUDA, "slab allocation of %zu bytes on device %d failed: %s", s.bytes, s.device,
+                cudaGetErrorString(e));
+      return fail();
+    }
+    s.d_pop = s.d_partials + kPopBlocks;
+    SlabState& h = s.h;
+    memset(&h, 0, sizeof h);
+    h.W = w->W;
+    h.H = w->H;
+    h.ws = w->ws;
+    h.stride = w->stride;
+    h.G = w->G;
+    h.rank = s.rank;
+    h.nranks = cfg->nranks;
+    for (int b = 0; b < 2; ++b) h.buf[b] = (uint64_t*)(s.base + s.off_buf[b]);
+    for (int side = 0; side < 2; ++side)
+      for (int p = 0; p < 2; ++p) h.recv[side][p] = (uint64_t*)(s.base + s.off_recv[side][p]);
+    h.flag[0] = (unsigned long long*)(s.base + s.off_flags);
+    h.flag[1] = (unsigned long long*)(s.base + s.off_flags + 128);
+    h.watchdog_ns = 10ull * 1000 * 1000 * 1000;
+  }
+  for (auto& g : w->groups) {
+    e = cudaSetDevice(g.device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking);
+    g.own_stream = (e == cudaSuccess);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&g.d_states, g.slabs.size() * sizeof(SlabState));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&g.d_barrier, 256);
+    if (e == cudaSuccess) e = cudaMemset(g.d_barrier, 0, 256);
+    if (e == cudaSuccess) e = cudaEventCreate(&g.e0);
+    if (e == cudaSuccess) e = cudaEventCreate(&g.e1);
+    if (e != cudaSuccess) {
+      set_error(GOL_ERR_CUDA, "device %d set-up failed: %s", g.device, cudaGetErrorString(e));
+      return fail();
+    }
+  }
+  if (finish_plan_cuda(w) != GOL_OK) return fail();
+  return w;
+}
+
+void gol_world_destroy(gol_world_t* w) {
+  if (!w) return;
+  if (w->cuda) {
+    for (auto& g : w->groups) {
+      cudaSetDevice(g.device);
+      if (g.stream) cudaStreamSynchronize(g.stream);
+      for (auto& kv : g.graphs) cudaGraphExecDestroy(kv.second.first);
+      if (g.e0) cudaEventDestroy(g.e0);
+      if (g.e1) cudaEventDestroy(g.e1);
+      if (g.d_states) cudaFree(g.d_states);
+      if (g.d_barrier) cudaFree(g.d_barrier);
+      if (g.own_stream && g.stream) cudaStreamDestroy(g.stream);
+    }
+    for (auto& p : w->peers)
+      if (p.ipc_opened && p.mapped) {
+        cudaSetDevice(p.opened_on);
+        cudaIpcCloseMemHandle(p.mapped);
+      }
+    for (auto& s : w->slabs) {
+      cudaSetDevice(s.device);
+      if (s.base) cudaFree(s.base);
+      if (s.d_partials) cudaFree(s.d_partials);
+    }
+  }
+  delete w;
+}
+
+int gol_world_plan(const gol_world_t* w, gol_plan_t* out) {
+  if (!w || !out) return set_error(GOL_ERR_ARG, "null argument");
+  *out = w->plan;
+  return GOL_OK;
+}
+
+int gol_world_export(gol_world_t* w, int li, void* blob) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!blob) return set_error(GOL_ERR_ARG, "null blob");
+  if (!w->cuda) return set_error(GOL_ERR_UNSUPPORTED, "export is for the CUDA backend");
+  Slab& s = w->slabs[(size_t)li];
+  ExportBlob b;
+  memset(&b, 0, sizeof b);
+  b.magic = kBlobMagic;
+  b.rank = s.rank;
+  b.device = s.device;
+  b.pid = (int32_t)getpid();
+  b.W = w->W;
+  b.H = w->H;
+  b.stride = w->stride;
+  b.G = w->G;
+  b.off_flags = s.off_flags;
+  for (int side = 0; side < 2; ++side)
+    for (int p = 0; p < 2; ++p) b.off_recv[side][p] = s.off_recv[side][p];
+  b.base_addr = (uint64_t)(uintptr_t)s.base;
+  CU_TRY(cudaSetDevice(s.device));
+  CU_TRY(cudaIpcGetMemHandle(&b.handle, s.base));
+  memset(blob, 0, GOL_EXPORT_BYTES);
+  memcpy(blob, &b, sizeof b);
+  return GOL_OK;
+}
+
+int gol_world_import(gol_world_t* w, int global_rank, const void* blob) {
+  if (!w || !blob) return set_error(GOL_ERR_ARG, "null argument");
+  if (global_rank < 0 || global_rank >= w->cfg.nranks)
+    return set_error(GOL_ERR_ARG, "rank %d out of range", global_rank);
+  ExportBlob b;
+  memcpy(&b, blob, sizeof b);
+  if (b.magic != kBlobMagic || b.rank != global_rank)
+    return set_error(GOL_ERR_ARG, "export blob for rank %d is malformed", global_rank);
+  if (b.W != w->W || b.H != w->H || b.stride != w->stride || b.G != w->G)
+    return set_error(GOL_ERR_ARG, "rank %d has a different slab geometry", global_rank);
+  Peer& p = w->peers[(size_t)global_rank];
+  p.blob = b;
+  p.imported = true;
+  p.mapped = nullptr;
+  return GOL_OK;
+}
+
+static int resolve_peer_base(gol_world* w, int rank, int for_device, char** base, ExportBlob* lay) {
+  // local slab?
+  for (auto& s : w->slabs)
+    if (s.rank == rank) {
+      if (s.device != for_device && !(w->cfg.flags & GOL_FLAG_NO_PEER_ACCESS)) {
+        int can = 0;
+        CU_TRY(cudaDeviceCanAccessPeer(&can, for_device, s.device));
+        if (!can)
+          return set_error(GOL_ERR_CUDA, "device %d cannot access device %d (no P2P path)", for_device, s.device);
+        CU_TRY(cudaSetDevice(for_device));
+        cudaError_t e = cudaDeviceEnablePeerAccess(s.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+          return set_error(GOL_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d->%d): %s", for_device, s.device,
+                           cudaGetErrorString(e));
+        cudaGetLastError();
+      }
+      *base = s.base;
+      lay->off_flags = s.off_flags;
+      for (int side = 0; side < 2; ++side)
+        for (int p = 0; p < 2; ++p) lay->off_recv[side][p] = s.off_recv[side][p];
+      return GOL_OK;
+    }
+  Peer& p = w->peers[(size_t)rank];
+  if (!p.imported) return set_error(GOL_ERR_STATE, "rank %d is neither local nor imported", rank);
+  if (!p.mapped) {
+    if (p.blob.pid == (int32_t)getpid()) {
+      p.mapped = (char*)(uintptr_t)p.blob.base_addr;  // another world in this process
+    } else {
+      CU_TRY(cudaSetDevice(for_device));
+      void* ptr = nullptr;
+      CU_TRY(cudaIpcOpenMemHandle(&ptr, p.blob.handle, cudaIpcMemLazyEnablePeerAccess));
+      p.mapped = (char*)ptr;
+      p.ipc_opened = true;
+      p.opened_on = for_device;
+    }
+  }
+  *base = p.mapped;
+  *lay = p.blob;
+  return GOL_OK;
+}
+
+int gol_world_connect(gol_world_t* w) {
+  if (!w) return set_error(GOL_ERR_ARG, "null world");
+  const int R = w->cfg.nranks;
+  if (!w->cuda) {
+    w->connected = true;
+    return GOL_OK;
+  }
+  for (auto& s : w->slabs) {
+    const int prev = (s.rank - 1 + R) % R;  // ring, gol-main.c:86-87
+    const int next = (s.rank + 1) % R;
+    char* pb = nullptr;
+    char* nb = nullptr;
+    ExportBlob pl{}, nl{};
+    int rc = resolve_peer_base(w, prev, s.device, &pb, &pl);
+    if (rc) return rc;
+    rc = resolve_peer_base(w, next, s.device, &nb, &nl);
+    if (rc) return rc;
+    for (int p = 0; p < 2; ++p) {
+      s.h.peer_recv[0][p] = (uint64_t*)(pb + pl.off_recv[1][p]);  // prev's bottom recv
+      s.h.peer_recv[1][p] = (uint64_t*)(nb + nl.off_recv[0][p]);  // next's top recv
+    }
+    s.h.peer_flag[0] = (unsigned long long*)(pb + pl.off_flags + 128);  // prev's bottom flag
+    s.h.peer_flag[1] = (unsigned long long*)(nb + nl.off_flags);        // next's top flag
+  }
+  int rc = upload_states(w);
+  if (rc) return rc;
+  w->connected = true;
+  return GOL_OK;
+}
+
+int gol_world_set_stream(gol_world_t* w, int li, void* stream) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!w->cuda) return GOL_OK;
+  Group& g = w->groups[(size_t)w->slabs[(size_t)li].group];
+  if ((cudaStream_t)stream == g.stream) return GOL_OK;
+  CU_TRY(cudaSetDevice(g.device));
+  if (g.stream) CU_TRY(cudaStreamSynchronize(g.stream));
+  if (g.own_stream && g.stream) cudaStreamDestroy(g.stream);
+  g.stream = (cudaStream_t)stream;
+  g.own_stream = false;
+  return GOL_OK;
+}
+
+int gol_world_init_pattern(gol_world_t* w, int pattern, uint64_t seed, double density) {
+  if (!w) return set_error(GOL_ERR_ARG, "null world");
+  for (auto& s : w->slabs) {
+    PatternArgs a;
+    int rc = make_pattern_args(&a, pattern, w->W, w->H, s.rank, w->cfg.nranks, seed, density);
+    if (rc) return rc;
+    if (!w->cuda) {
+      uint64_t* dst = s.cbuf[s.ccur].data();
+      for (int64_t y = 0; y < w->H; ++y)
+        for (int64_t x = 0; x < w->stride; ++x)
+          dst[y * w->stride + x] = x < w->ws ? pattern_word(a, y, x) : 0ull;
+    } else {
+      Group& g = w->groups[(size_t)s.group];
+      CU_TRY(cudaSetDevice(s.device));
+      CU_TRY(launch_pattern_init(cur_interior(w, s), w->stride, a, g.stream));
+    }
+  }
+  return GOL_OK;
+}
+
+int gol_world_load_packed_async(gol_world_t* w, int li, const uint64_t* words) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!words) return set_error(GOL_ERR_ARG, "null buffer");
+  Slab& s = w->slabs[(size_t)li];
+  const size_t n = (size_t)(w->H * w->stride) * 8;
+  if (!w->cuda) {
+    memcpy(s.cbuf[s.ccur].data(), words, n);
+    return GOL_OK;
+  }
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  CU_TRY(cudaMemcpyAsync(cur_interior(w, s), words, n, cudaMemcpyHostToDevice, g.stream));
+  return GOL_OK;
+}
+
+int gol_world_load_packed(gol_world_t* w, int li, const uint64_t* words) {
+  int rc = gol_world_load_packed_async(w, li, words);
+  if (rc) return rc;
+  if (w->cuda) CU_TRY(cudaStreamSynchronize(w->groups[(size_t)w->slabs[(size_t)li].group].stream));
+  return GOL_OK;
+}
+
+int gol_world_load_bytes(gol_world_t* w, int li, const uint8_t* cells) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!cells) return set_error(GOL_ERR_ARG, "null buffer");
+  Slab& s = w->slabs[(size_t)li];
+  if (!w->cuda) return gol_pack_bytes(cells, s.cbuf[s.ccur].data(), w->W, w->H);
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  uint8_t* d = nullptr;
+  const size_t n = (size_t)w->W * (size_t)w->H;
+  CU_TRY(cudaMalloc((void**)&d, n));
+  cudaError_t e = cudaMemcpyAsync(d, cells, n, cudaMemcpyHostToDevice, g.stream);
+  if (e == cudaSuccess) e = launch_pack(d, cur_interior(w, s), w->W, w->H, w->stride, g.stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "load_bytes: %s", cudaGetErrorString(e));
+  return GOL_OK;
+}
+
+int gol_world_read_packed(gol_world_t* w, int li, uint64_t* words) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!words) return set_error(GOL_ERR_ARG, "null buffer");
+  Slab& s = w->slabs[(size_t)li];
+  const size_t n = (size_t)(w->H * w->stride) * 8;
+  if (!w->cuda) {
+    memcpy(words, s.cbuf[s.ccur].data(), n);
+    return GOL_OK;
+  }
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  CU_TRY(cudaMemcpyAsync(words, cur_interior(w, s), n, cudaMemcpyDeviceToHost, g.stream));
+  CU_TRY(cudaStreamSynchronize(g.stream));
+  return GOL_OK;
+}
+
+int gol_world_read_bytes(gol_world_t* w, int li, uint8_t* cells) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!cells) return set_error(GOL_ERR_ARG, "null buffer");
+  Slab& s = w->slabs[(size_t)li];
+  if (!w->cuda) return gol_unpack_words(s.cbuf[s.ccur].data(), cells, w->W, w->H);
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  uint8_t* d = nullptr;
+  const size_t n = (size_t)w->W * (size_t)w->H;
+  CU_TRY(cudaMalloc((void**)&d, n));
+  cudaError_t e = launch_unpack(cur_interior(w, s), d, w->W, w->H, w->stride, g.stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(cells, d, n, cudaMemcpyDeviceToHost, g.stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "read_bytes: %s", cudaGetErrorString(e));
+  return GOL_OK;
+}
+
+int gol_world_population_async(gol_world_t* w, int li, uint64_t* out) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!out) return set_error(GOL_ERR_ARG, "null output");
+  Slab& s = w->slabs[(size_t)li];
+  if (!w->cuda) {
+    uint64_t t = 0;
+    const uint64_t* p = s.cbuf[s.ccur].data();
+    for (int64_t y = 0; y < w->H; ++y)
+      for (int64_t x = 0; x < w->ws; ++x) t += (uint64_t)__builtin_popcountll(p[y * w->stride + x]);
+    *out = t;
+    return GOL_OK;
+  }
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  CU_TRY(launch_population(cur_interior(w, s), w->ws, w->stride, w->H, s.d_partials, s.d_pop, g.stream));
+  CU_TRY(cudaMemcpyAsync(out, s.d_pop, sizeof(uint64_t), cudaMemcpyDeviceToHost, g.stream));
+  return GOL_OK;
+}
+
+int gol_world_population(gol_world_t* w, int li, uint64_t* out) {
+  int rc = gol_world_population_async(w, li, out);
+  if (rc) return rc;
+  if (w->cuda) CU_TRY(cudaStreamSynchronize(w->groups[(size_t)w->slabs[(size_t)li].group].stream));
+  return GOL_OK;
+}
+
+static int step_cuda(gol_world* w, int64_t gens) {
+  const gol_plan_t& pl = w->plan;
+  const bool use_graph = !(w->cfg.flags & GOL_FLAG_NO_GRAPH);
+  int64_t todo = gens;
+
+  if (pl.mode == GOL_MODE_PERSISTENT) {
+    const int P = pl.exchange_depth / pl.temporal_k;
+    const int64_t periods = todo / pl.exchange_depth;
+    if (periods > 0) {
+      const int64_t max_periods = (int64_t)(1 << 20);
+      int64_t left = periods;
+      while (left > 0) {
+        const int64_t now = std::min(left, max_periods);
+        for (auto& g : w->groups) {
+          CU_TRY(cudaSetDevice(g.device));
+          PersistentParams pp;
+          memset(&pp, 0, sizeof pp);
+          pp.pass.ext_in = pl.exchange_depth;
+          pp.pass.k = pl.temporal_k;
+          pp.pass.strip_rows = pl.strip_rows;
+          pp.pass.col_groups = pl.col_groups;
+          pp.npasses = (int)(now * P);
+          pp.passes_per_exchange = P;
+          pp.depth = pl.exchange_depth;
+          pp.nslabs = (int)g.slabs.size();
+          pp.barrier = g.d_barrier;
+          const int wpb = pl.threads_per_block / 32;
+          const int64_t rows_total = w->H + 2 * (pl.exchange_depth - pl.temporal_k);
+          const int64_t tasks = ((rows_total + pl.strip_rows - 1) / pl.strip_rows) * pl.col_groups;
+          int nctas = persistent_max_ctas(pl.temporal_k, pl.threads_per_block, g.device);
+          if (nctas < 1) return set_error(GOL_ERR_CUDA, "persistent kernel cannot be made resident");
+          nctas = (int)std::min<int64_t>(nctas, (tasks + wpb - 1) / wpb);
+          CU_TRY(cudaMemsetAsync(g.d_barrier, 0, 8, g.stream));
+          CU_TRY(launch_persistent(pl.temporal_k, g.d_states, pp, pl.threads_per_block, nctas, g.stream));
+        }
+        w->pass_host += (uint64_t)(now * P);
+        left -= now;
+      }
+      todo -= periods * pl.exchange_depth;
+    }
+    if (todo == 0) return GOL_OK;
+  }
+
+  const std::vector<PassItem> items = build_schedule(w, todo);
+  if (items.empty()) return GOL_OK;
+  const int npass = count_passes(items);
+  if (use_graph && items.size() > 2) {
+    for (auto& g : w->groups) {
+      CU_TRY(cudaSetDevice(g.device));
+      auto it = g.graphs.find(todo);
+      if (it == g.graphs.end()) {
+        const uint64_t before = launch_count_value();
+        cudaGraph_t graph = nullptr;
+        CU_TRY(cudaStreamBeginCapture(g.stream, cudaStreamCaptureModeThreadLocal));
+        int rc = GOL_OK;
+        for (auto& item : items) {
+          rc = launch_item(w, g, item);
+          if (rc) break;
+        }
+        cudaError_t e = cudaStreamEndCapture(g.stream, &graph);
+        count_launch(before - launch_count_value());  // capture is not execution
+        if (rc) {
+          if (graph) cudaGraphDestroy(graph);
+          return rc;
+        }
+        if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
+        cudaGraphExec_t exec = nullptr;
+        e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph instantiate failed: %s", cudaGetErrorString(e));
+        if (g.graphs.size() > 16) {
+          for (auto& kv : g.graphs) cudaGraphExecDestroy(kv.second.first);
+          g.graphs.clear();
+        }
+        it = g.graphs.emplace(todo, std::make_pair(exec, (int)items.size())).first;
+      }
+      CU_TRY(cudaGraphLaunch(it->second.first, g.stream));
+      count_launch((uint64_t)it->second.second);
+    }
+  } else {
+    for (auto& item : items)
+      for (auto& g : w->groups) {
+        CU_TRY(cudaSetDevice(g.device));
+        int rc = launch_item(w, g, item);
+        if (rc) return rc;
+      }
+  }
+  w->pass_host += (uint64_t)npass;
+  return GOL_OK;
+}
+
+int gol_world_step(gol_world_t* w, int64_t gens) {
+  if (!w) return set_error(GOL_ERR_ARG, "null world");
+  if (gens < 0) return set_error(GOL_ERR_ARG, "negative generation count");
+  if (gens == 0) return GOL_OK;
+  if (!w->cuda) {
+    if ((int)w->slabs.size() != w->cfg.nranks)
+      return set_error(GOL_ERR_STATE,
+                       "CPU world owns %d of %d ranks: drive it with cpu_get_edge / cpu_set_ghost / cpu_step_local",
+                       (int)w->slabs.size(), w->cfg.nranks);
+    for (int64_t g = 0; g < gens; ++g) {
+      cpu_exchange_local(w);
+      for (auto& s : w->slabs) cpu_step_slab(w, s);
+    }
+    return GOL_OK;
+  }
+  if (!w->connected) return set_error(GOL_ERR_STATE, "gol_world_connect has not been called");
+  return step_cuda(w, gens);
+}
+
+int gol_world_sync(gol_world_t* w) {
+  if (!w) return set_error(GOL_ERR_ARG, "null world");
+  if (!w->cuda) return GOL_OK;
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    CU_TRY(cudaStreamSynchronize(g.stream));
+  }
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    std::vector<SlabState> hs(g.slabs.size());
+    CU_TRY(cudaMemcpy(hs.data(), g.d_states, hs.size() * sizeof(SlabState), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < hs.size(); ++i) {
+      if (hs[i].error)
+        return set_error(GOL_ERR_TIMEOUT,
+                         "rank %d: halo from the %s neighbour did not arrive within the watchdog (device error %d)",
+                         hs[i].rank, hs[i].error == 1 ? "previous" : "next", hs[i].error);
+      if (w->connected && hs[i].pass != w->pass_host)
+        return set_error(GOL_ERR_STATE, "rank %d: device pass counter %llu != host %llu", hs[i].rank,
+                         hs[i].pass, (unsigned long long)w->pass_host);
+    }
+  }
+  return GOL_OK;
+}
+
+int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms) {
+  if (!w || !ms) return set_error(GOL_ERR_ARG, "null argument");
+  if (!w->cuda) {
+    timespec a, b;
+    clock_gettime(CLOCK_MONOTONIC, &a);
+    int rc = gol_world_step(w, gens);
+    clock_gettime(CLOCK_MONOTONIC, &b);
+    const float t = (float)((b.tv_sec - a.tv_sec) * 1e3 + (b.tv_nsec - a.tv_nsec) * 1e-6);
+    for (size_t i = 0; i < w->slabs.size(); ++i) ms[i] = t;
+    return rc;
+  }
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    CU_TRY(cudaEventRecord(g.e0, g.stream));
+  }
+  int rc = gol_world_step(w, gens);
+  if (rc) return rc;
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    CU_TRY(cudaEventRecord(g.e1, g.stream));
+  }
+  rc = gol_world_sync(w);
+  if (rc) return rc;
+  for (auto& g : w->groups) {
+    float t = 0;
+    CU_TRY(cudaSetDevice(g.device));
+    CU_TRY(cudaEventElapsedTime(&t, g.e0, g.e1));
+    for (int si : g.slabs) ms[si] = t;
+  }
+  return GOL_OK;
+}
+
+void* gol_world_device_ptr(gol_world_t* w, int li) {
+  if (check_local(w, li) != GOL_OK) return nullptr;
+  Slab& s = w->slabs[(size_t)li];
+  if (!w->cuda) return s.cbuf[s.ccur].data();
+  return cur_interior(w, s);
+}
+
+int gol_world_device_of(gol_world_t* w, int li) {
+  if (check_local(w, li) != GOL_OK) return -1;
+  return w->cuda ? w->slabs[(size_t)li].device : -1;
+}
+
+int gol_world_cpu_get_edge(gol_world_t* w, int li, int bottom, uint64_t* row) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (w->cuda || !row) return set_error(GOL_ERR_ARG, "cpu_get_edge needs a CPU world and a buffer");
+  Slab& s = w->slabs[(size_t)li];
+  const uint64_t* src = s.cbuf[s.ccur].data() + (bottom ? (w->H - 1) * w->stride : 0);
+  memcpy(row, src, (size_t)w->stride * 8);
+  return GOL_OK;
+}
+
+int gol_world_cpu_set_ghost(gol_world_t* w, int li, int bottom, const uint64_t* row) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (w->cuda || !row) return set_error(GOL_ERR_ARG, "cpu_set_ghost needs a CPU world and a buffer");
+  memcpy(w->slabs[(size_t)li].cghost[bottom ? 1 : 0].data(), row, (size_t)w->stride * 8);
+  return GOL_OK;
+}
+
+int gol_world_cpu_step_local(gol_world_t* w) {
+  if (!w || w->cuda) return set_error(GOL_ERR_ARG, "cpu_step_local needs a CPU world");
+  for (auto& s : w->slabs) cpu_step_slab(w, s);
+  return GOL_OK;
+}
+
+int gol_world_dump_text(gol_world_t* w, int li, const char* dir) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  Slab& s = w->slabs[(size_t)li];
+  char name[64];
+  gol_rank_file_name(name, sizeof name, s.rank, w->cfg.nranks);
+  std::string path = (dir && *dir) ? std::string(dir) + "/" + name : std::string(name);
+  if (!w->cuda) {
+    std::vector<uint8_t> cells((size_t)w->W * (size_t)w->H);
+    rc = gol_unpack_words(s.cbuf[s.ccur].data(), cells.data(), w->W, w->H);
+    if (rc) return rc;
+    return gol_write_rank_file(path.c_str(), cells.data(), w->W, w->H, s.rank);
+  }
+  // device-formatted rows, streamed in chunks
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  const int64_t pitch = (int64_t)align_up((size_t)(kTextCellOff + 2 * w->W + 1), 16);
+  int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(64ll << 20) / pitch);
+  chunk_rows = std::min(chunk_rows, w->H);
+  char* d_text = nullptr;
+  char* h_text = nullptr;
+  CU_TRY(cudaMalloc((void**)&d_text, (size_t)(chunk_rows * pitch)));
+  cudaError_t e = cudaMallocHost((void**)&h_text, (size_t)(chunk_rows * pitch));
+  if (e != cudaSuccess) {
+    cudaFree(d_text);
+    return set_error(GOL_ERR_CUDA, "pinned allocation failed: %s", cudaGetErrorString(e));
+  }
+  FILE* fp = fopen(path.c_str(), "w");
+  if (!fp) {
+    cudaFree(d_text);
+    cudaFreeHost(h_text);
+    return set_error(GOL_ERR_IO, "cannot open %s: %s", path.c_str(), strerror(errno));
+  }
+  rc = write_rank_header(fp, s.rank);
+  const uint64_t* rows = cur_interior(w, s);
+  for (int64_t y0 = 0; y0 < w->H && rc == GOL_OK; y0 += chunk_rows) {
+    const int64_t n = std::min(chunk_rows, w->H - y0);
+    const int64_t first_global = w->H * s.rank + y0;
+    e = launch_format_rows(rows + y0 * w->stride, w->stride, w->W, n, first_global, d_text, pitch, g.stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(h_text, d_text, (size_t)(n * pitch), cudaMemcpyDeviceToHost, g.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+    if (e != cudaSuccess) {
+      rc = set_error(GOL_ERR_CUDA, "format_rows: %s", cudaGetErrorString(e));
+      break;
+    }
+    for (int64_t r = 0; r < n; ++r) {
+      char pre[40];
+      const int plen = snprintf(pre, sizeof pre, "Row %2d: ", (int)(first_global + r));
+      const char* start = h_text + r * pitch + kTextCellOff - plen;
+      const size_t len = (size_t)plen + (size_t)(2 * w->W) + 1;
+      if (fwrite(start, 1, len, fp) != len) {
+        rc = set_error(GOL_ERR_IO, "short write to %s", path.c_str());
+        break;
+      }
+    }
+  }
+  if (fclose(fp) != 0 && rc == GOL_OK) rc = set_error(GOL_ERR_IO, "close of %s failed", path.c_str());
+  cudaFree(d_text);
+  cudaFreeHost(h_text);
+  return rc;
+}
+
+// ---- stateless device ops -------------------------------------------------------
+int gol_cuda_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H, void* stream) {
+  if (!d_cells || !d_words || W < 1 || H < 1) return set_error(GOL_ERR_ARG, "gol_cuda_pack: bad argument");
+  CU_TRY(launch_pack(d_cells, d_words, W, H, row_stride_words(W), (cudaStream_t)stream));
+  return GOL_OK;
+}
+
+int gol_cuda_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H, void* stream) {
+  if (!d_cells || !d_words || W < 1 || H < 1) return set_error(GOL_ERR_ARG, "gol_cuda_unpack: bad argument");
+  CU_TRY(launch_unpack(d_words, d_cells, W, H, row_stride_words(W), (cudaStream_t)stream));
+  return GOL_OK;
+}
+
+size_t gol_cuda_population_scratch_bytes(void) { return kPopBlocks * sizeof(unsigned long long); }
+
+int gol_cuda_population(const uint64_t* d_words, int64_t W, int64_t H, void* d_scratch, uint64_t* d_out,
+                        void* stream) {
+  if (!d_words || !d_scratch || !d_out || W < 1 || H < 1)
+    return set_error(GOL_ERR_ARG, "gol_cuda_population: bad argument");
+  CU_TRY(launch_population(d_words, words_per_row(W), row_stride_words(W), H, (unsigned long long*)d_scratch,
+                           (unsigned long long*)d_out, (cudaStream_t)stream));
+  return GOL_OK;
+}
+
+int gol_cuda_step_torus(const uint64_t* d_in, uint64_t* d_out, int64_t W, int64_t H, int threads, void* stream) {
+  if (!d_in || !d_out || d_in == d_out || W < 1 || H < 1)
+    return set_error(GOL_ERR_ARG, "gol_cuda_step_torus: bad argument");
+  if (threads <= 0) threads = 256;
+  if (threads > 1024) return set_error(GOL_ERR_ARG, "threads per block must be <= 1024");
+  const int64_t st = row_stride_words(W);
+  CU_TRY(launch_step_rows(d_in, d_out, d_in + (H - 1) * st, d_in, W, H, st, threads, (cudaStream_t)stream));
+  return GOL_OK;
+}
+
+int gol_cuda_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_top, const uint64_t* d_bottom,
+                       int64_t W, int64_t H, int threads, void* stream) {
+  if (!d_in || !d_out || !d_top || !d_bottom || d_in == d_out || W < 1 || H < 1)
+    return set_error(GOL_ERR_ARG, "gol_cuda_step_rows: bad argument");
+  if (threads <= 0) threads = 256;
+  if (threads > 1024) return set_error(GOL_ERR_ARG, "threads per block must be <= 1024");
+  CU_TRY(launch_step_rows(d_in, d_out, d_top, d_bottom, W, H, row_stride_words(W), threads, (cudaStream_t)stream));
+  return GOL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,160 @@
+"""`Life`: the user-facing stepper.
+
+Two rank models, both producing the reference's ``Rank_<r>_of_<R>.txt`` files:
+
+* **single process** (``ranks=R``): one process drives R slabs, one per GPU
+  (or several per GPU when R exceeds the device count), ring neighbours reached
+  through NVLink peer pointers;
+* **process per GPU** (``torchrun``): parity with the reference's MPI model
+  (gol-main.c:58-62).  ``torch.distributed`` is used only to bootstrap: ranks
+  all-gather CUDA-IPC handles once, after which every halo row travels as a
+  direct store into the neighbour's memory from inside the step kernel.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import numpy as np
+
+from .. import _native
+from .._native import World
+
+
+def _dist():
+    import torch.distributed as dist
+
+    return dist if dist.is_available() and dist.is_initialized() else None
+
+
+class Life:
+    def __init__(self, size: int, rows: Optional[int] = None, *, ranks: Optional[int] = None,
+                 backend: str = "cuda", mode: str = "auto", k: int = 0, depth: int = 0, threads: int = 0,
+                 distributed: Optional[bool] = None, flags: int = 0):
+        self.width = int(size)
+        self.rows = int(rows if rows is not None else size)
+        dist = _dist()
+        if distributed is None:
+            distributed = dist is not None and dist.get_world_size() > 1 and ranks is None
+        self.distributed = bool(distributed)
+        if self.distributed:
+            if dist is None:
+                raise _native.GolError("distributed=True needs an initialised torch.distributed group")
+            self.nranks = dist.get_world_size()
+            self.rank = dist.get_rank()
+            local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+            self.world = World(self.width, self.rows, nranks=self.nranks, first_rank=self.rank, nlocal=1,
+                               backend=backend, mode=mode, k=k, depth=depth, threads=threads,
+                               device_base=local_rank, flags=flags)
+            if backend == "cuda":
+                from ..parallel.peer import connect_over_dist
+
+                connect_over_dist(self.world)
+            self._cpu_ring = None
+            if backend != "cuda":
+                from ..parallel.gloo_cpu import GlooRing
+
+                self._cpu_ring = GlooRing(self.world)
+        else:
+            self.nranks = int(ranks or 1)
+            self.rank = 0
+            self.world = World(self.width, self.rows, nranks=self.nranks, backend=backend, mode=mode, k=k,
+                               depth=depth, threads=threads, flags=flags)
+            self.world.connect()
+            self._cpu_ring = None
+        self.backend = backend
+        self.generation = 0
+
+    # ------------------------------------------------------------------ state
+    @property
+    def plan(self) -> dict:
+        return self.world.plan
+
+    @property
+    def local_ranks(self) -> List[int]:
+        return list(range(self.world.first_rank, self.world.first_rank + self.world.nlocal))
+
+    def init(self, pattern: int, seed: int = 1, density: float = 0.5) -> "Life":
+        self.world.init_pattern(pattern, seed, density)
+        self.generation = 0
+        return self
+
+    def load(self, cells: np.ndarray, local: int = 0) -> "Life":
+        self.world.load_bytes(local, cells)
+        return self
+
+    def load_packed(self, words, local: int = 0, asynchronous: bool = False) -> "Life":
+        self.world.load_packed(local, words, asynchronous=asynchronous)
+        return self
+
+    def cells(self, local: int = 0) -> np.ndarray:
+        return self.world.read_bytes(local)
+
+    def all_local_cells(self) -> np.ndarray:
+        return np.concatenate([self.world.read_bytes(i) for i in range(self.world.nlocal)], axis=0)
+
+    # --------------------------------------------------------------- stepping
+    def step(self, generations: int = 1) -> "Life":
+        if self._cpu_ring is not None:
+            self._cpu_ring.step(generations)
+        else:
+            self.world.step(generations)
+        self.generation += generations
+        return self
+
+    def sync(self) -> "Life":
+        self.world.sync()
+        return self
+
+    def step_timed(self, generations: int) -> float:
+        """Device-timed step: milliseconds, max over this process's slabs and over all ranks."""
+        if self._cpu_ring is not None:
+            import time
+
+            t0 = time.perf_counter()
+            self._cpu_ring.step(generations)
+            ms = (time.perf_counter() - t0) * 1e3
+        else:
+            ms = max(self.world.step_timed(generations))
+        self.generation += generations
+        dist = _dist()
+        if self.distributed and dist is not None:
+            import torch
+
+            dev = "cuda" if (self.backend == "cuda" and dist.get_backend() == "nccl") else "cpu"
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---------------------------------------------------------------- metrics
+    def population(self, global_sum: bool = True) -> int:
+        n = sum(self.world.population(i) for i in range(self.world.nlocal))
+        dist = _dist()
+        if global_sum and self.distributed and dist is not None:
+            import torch
+
+            dev = "cuda" if (self.backend == "cuda" and dist.get_backend() == "nccl") else "cpu"
+            t = torch.tensor([n], dtype=torch.int64, device=dev)
+            dist.all_reduce(t)
+            n = int(t.item())
+        return n
+
+    def cell_updates(self, iterations: int) -> int:
+        return self.nranks * self.rows * self.width * iterations  # gol-main.c:124-125
+
+    # --------------------------------------------------------------------- io
+    def dump(self, directory: Optional[str] = None) -> List[str]:
+        """Write ``Rank_<r>_of_<R>.txt`` for every local slab (gol-main.c:135-139)."""
+        names = []
+        for i, r in enumerate(self.local_ranks):
+            self.world.dump_text(i, directory)
+            names.append(os.path.join(directory or ".", _native.rank_file_name(r, self.nranks)))
+        return names
+
+    def report(self, seconds: float, iterations: int) -> str:
+        """The two stdout lines of rank 0 (gol-main.c:124-125,132)."""
+        return _native.format_report(seconds, self.nranks, self.width, self.rows, iterations)
+
+    def close(self) -> None:
+        self.world.close()

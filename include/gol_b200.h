@@ -1,0 +1,184 @@
+/* gol_b200.h — C ABI of the B200-native distributed Game-of-Life core.
+ *
+ * Everything a driver needs (the `gol` CLI, the Python/PyTorch layer, a third
+ * party) goes through this header.  All functions return 0 on success and a
+ * negative code on failure unless stated otherwise; gol_last_error() gives the
+ * message of the last failure on the calling thread.
+ *
+ * Geometry (same as the reference, gol-main.c:22,76): rank r of R owns global
+ * rows [r*H, (r+1)*H) of a W-wide, H*R-tall torus.  Cells are stored bit-packed,
+ * 64 per uint64 word, bit j of word w of a row = column 64*w + j.
+ */
+#ifndef GOL_B200_H_
+#define GOL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GOL_OK 0
+#define GOL_ERR_ARG (-1)
+#define GOL_ERR_CUDA (-2)
+#define GOL_ERR_STATE (-3)
+#define GOL_ERR_IO (-4)
+#define GOL_ERR_TIMEOUT (-5)
+#define GOL_ERR_UNSUPPORTED (-6)
+
+#define GOL_BACKEND_CPU 0
+#define GOL_BACKEND_CUDA 1
+
+/* step-kernel selection */
+#define GOL_MODE_AUTO 0        /* fused where the shape allows, else generic   */
+#define GOL_MODE_GENERIC 1     /* one thread per word, any W/H, 1 gen per pass  */
+#define GOL_MODE_FUSED 2       /* register-streaming, K generations per pass    */
+#define GOL_MODE_PERSISTENT 3  /* one cooperative launch for the whole step()   */
+#define GOL_MODE_TMA 4         /* fused, input rows fed by TMA bulk copies      */
+
+#define GOL_MAX_GHOST 32       /* deepest exchange (rows per side)              */
+
+const char* gol_last_error(void);
+const char* gol_version(void);
+
+/* ---- CPU oracle and helpers (no GPU needed) ------------------------------ */
+
+/* True torus Life on a W x H byte grid (0/1 per cell), `gens` generations.
+ * Restates the reference kernel's neighbourhood and rule
+ * (gol-with-cuda.cu:207-257) for the whole global grid; this is the oracle. */
+int gol_oracle_run(const uint8_t* in, uint8_t* out, int64_t W, int64_t H, int64_t gens);
+
+/* Fill one rank's W x H byte slab with pattern 0..6 (gol-with-cuda.cu:56-171
+ * for 0..4; 5 = glider, 6 = random density).  density in [0,1]. */
+int gol_pattern_fill_bytes(uint8_t* cells, int pattern, int64_t W, int64_t H,
+                           int rank, int nranks, uint64_t seed, double density);
+
+/* bytes <-> packed words (row stride = gol_row_stride_words(W)). */
+int64_t gol_words_per_row(int64_t W);
+int64_t gol_row_stride_words(int64_t W);
+int gol_pack_bytes(const uint8_t* cells, uint64_t* words, int64_t W, int64_t H);
+int gol_unpack_words(const uint64_t* words, uint8_t* cells, int64_t W, int64_t H);
+
+/* Bit-packed CPU torus stepper on the whole grid (timed CPU baseline). */
+int gol_cpu_run_packed(uint64_t* words, int64_t W, int64_t H, int64_t gens);
+
+/* Text of one rank's final world exactly as the reference writes it
+ * (gol-main.c:17-28,135-139): header line, then "Row %2d: " + "%u " per cell.
+ * gol_write_rank_file creates/truncates `path`. */
+int gol_write_rank_file(const char* path, const uint8_t* cells, int64_t W, int64_t H,
+                        int rank);
+/* "Rank_<r>_of_<R>.txt" (gol-main.c:66). buf must hold >= 64 bytes. */
+int gol_rank_file_name(char* buf, size_t n, int rank, int nranks);
+/* The two stdout lines of rank 0 (gol-main.c:124-125,132) into buf. */
+int gol_format_report(char* buf, size_t n, double seconds, int nranks, int64_t W, int64_t H,
+                      int64_t iterations);
+
+/* ---- world: slabs + ring + stepping --------------------------------------- */
+
+typedef struct gol_world gol_world_t;
+
+typedef struct gol_config {
+  int64_t width;          /* W: columns                                         */
+  int64_t rows;           /* H: rows per rank                                   */
+  int32_t nranks;         /* R: ranks in the ring                               */
+  int32_t first_rank;     /* this process owns ranks [first_rank, +nlocal)      */
+  int32_t nlocal;
+  int32_t backend;        /* GOL_BACKEND_*                                      */
+  int32_t mode;           /* GOL_MODE_*                                         */
+  int32_t temporal_k;     /* generations per pass (1,2,4,8); 0 = default        */
+  int32_t exchange_depth; /* rows per halo exchange (multiple of k); 0 = k      */
+  int32_t threads_per_block; /* CLI arg 4 (gol-main.c:52); 0 = default          */
+  int32_t ndevices;       /* devices to spread local ranks over; 0 = all        */
+  int32_t device_base;    /* local rank i -> device (device_base+i) % ndevices  */
+  int32_t flags;          /* GOL_FLAG_*                                         */
+  int32_t reserved;
+} gol_config_t;
+
+#define GOL_FLAG_NO_GRAPH 1      /* launch passes one by one, no CUDA graph     */
+#define GOL_FLAG_NO_PEER_ACCESS 2 /* do not call cudaDeviceEnablePeerAccess     */
+
+gol_world_t* gol_world_create(const gol_config_t* cfg);
+void gol_world_destroy(gol_world_t* w);
+
+/* What the planner chose (mode after AUTO resolution, k, depth, block size). */
+typedef struct gol_plan {
+  int32_t mode, temporal_k, exchange_depth, threads_per_block;
+  int32_t strip_rows, col_groups, ctas_per_slab, regs_hint;
+  int64_t words_per_row, row_stride, slab_rows;
+} gol_plan_t;
+int gol_world_plan(const gol_world_t* w, gol_plan_t* out);
+
+/* Multi-process wiring.  Each process exports one blob per local rank, all
+ * ranks gather them (torch.distributed / any transport) and import the ones
+ * they do not own; gol_world_connect() then resolves every local slab's ring
+ * neighbours (local pointer, P2P pointer or CUDA-IPC mapping).  With all ranks
+ * local, call gol_world_connect() directly. */
+#define GOL_EXPORT_BYTES 256
+int gol_world_export(gol_world_t* w, int local_index, void* blob /* GOL_EXPORT_BYTES */);
+int gol_world_import(gol_world_t* w, int global_rank, const void* blob);
+int gol_world_connect(gol_world_t* w);
+
+/* Streams: by default one non-blocking stream per device created by the world.
+ * gol_world_set_stream lets PyTorch hand in its current stream. */
+int gol_world_set_stream(gol_world_t* w, int local_index, void* cuda_stream);
+
+/* State.  All of these enqueue on the slab's stream (CUDA) or run inline (CPU). */
+int gol_world_init_pattern(gol_world_t* w, int pattern, uint64_t seed, double density);
+int gol_world_load_bytes(gol_world_t* w, int local_index, const uint8_t* cells);      /* host, W*H */
+int gol_world_load_packed(gol_world_t* w, int local_index, const uint64_t* words);    /* host, H*stride */
+int gol_world_read_bytes(gol_world_t* w, int local_index, uint8_t* cells);            /* host out */
+int gol_world_read_packed(gol_world_t* w, int local_index, uint64_t* words);          /* host out */
+int gol_world_population(gol_world_t* w, int local_index, uint64_t* count);           /* syncs */
+/* async pieces for end-to-end pipelines: result lands in *pinned_out after the stream drains */
+int gol_world_load_packed_async(gol_world_t* w, int local_index, const uint64_t* pinned_words);
+int gol_world_population_async(gol_world_t* w, int local_index, uint64_t* pinned_out);
+
+/* Advance every local slab by `gens` generations (halo exchange fused in).
+ * Asynchronous on CUDA; gol_world_sync waits and reports device-side errors
+ * (flag-wait watchdog, bad launch). */
+int gol_world_step(gol_world_t* w, int64_t gens);
+int gol_world_sync(gol_world_t* w);
+/* Same, bracketed by CUDA events: ms[i] = device time of local slab i's stream. */
+int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms /* nlocal */);
+
+/* Device pointer of the current packed slab interior (row 0, word 0) for
+ * zero-copy views; stride in words via gol_world_plan(). */
+void* gol_world_device_ptr(gol_world_t* w, int local_index);
+int gol_world_device_of(gol_world_t* w, int local_index);
+
+/* CPU-backend hooks for an external transport (gloo/MPI) when not all ranks
+ * are local: read my edge rows, write my ghost rows, step once. */
+int gol_world_cpu_get_edge(gol_world_t* w, int local_index, int bottom, uint64_t* row /* stride */);
+int gol_world_cpu_set_ghost(gol_world_t* w, int local_index, int bottom, const uint64_t* row);
+int gol_world_cpu_step_local(gol_world_t* w);
+
+/* Write Rank_<r>_of_<R>.txt for a local slab into directory `dir` (NULL = cwd);
+ * on CUDA the row text is formatted on the device (gol-main.c:17-28 layout). */
+int gol_world_dump_text(gol_world_t* w, int local_index, const char* dir);
+
+/* Kernels launched by this library in this process (graph replays counted per node). */
+uint64_t gol_launch_count(void);
+
+/* ---- stateless device ops on caller-owned buffers (stream = cudaStream_t) -- */
+int gol_cuda_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H, void* stream);
+int gol_cuda_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H, void* stream);
+/* Population of H rows of packed words.  d_scratch: >= gol_cuda_population_scratch_bytes()
+ * bytes of device memory (per-block partial sums); d_out: one uint64. */
+size_t gol_cuda_population_scratch_bytes(void);
+int gol_cuda_population(const uint64_t* d_words, int64_t W, int64_t H, void* d_scratch,
+                        uint64_t* d_out, void* stream);
+/* One torus generation of a stand-alone packed W x H grid (no ring): out != in. */
+int gol_cuda_step_torus(const uint64_t* d_in, uint64_t* d_out, int64_t W, int64_t H,
+                        int threads_per_block, void* stream);
+/* One generation of an H-row slab with explicit ghost rows above / below (each one
+ * packed row).  This is the unfused stencil the NCCL-halo baseline uses after its
+ * ncclSend/ncclRecv exchange; the product path fuses both (gol_world_step). */
+int gol_cuda_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_top,
+                       const uint64_t* d_bottom, int64_t W, int64_t H, int threads_per_block,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GOL_B200_H_ */
