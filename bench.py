@@ -1,0 +1,267 @@
+#!/usr/bin/env python
+"""Headline benchmark: cell updates per second (GCUPS) on N B200s, device-timed, max over ranks.
+
+Config (BASELINE.json #2): 16384 x 16384 cells per GPU, random 50 % density, weak scaling; one
+"step" = 1024 generations of the whole torus (halo exchange every k generations fused into the
+step kernel).  `--impl reference` runs the UNMODIFIED reference binary built by
+baseline/build_ref.sh (its own MPI+CUDA code path, `mpirun -n N gol 1 16384 <gens> 512 0`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SIZE = 16384
+GENS_PER_STEP = 1024
+METRIC = "cell updates/sec (GCUPS, device-timed, max over ranks)"
+
+
+def env_rank():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+
+
+# ---------------------------------------------------------------------------- reference arm
+def run_reference(args) -> int:
+    rank, world, _ = env_rank()
+    if world > 1:
+        # launched under torchrun like our arm: rank 0 drives the reference's own launcher
+        import torch.distributed as dist
+
+        dist.init_process_group("gloo")
+    out = {"impl": "reference"}
+    if rank == 0:
+        out = reference_measure(args)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    return 0
+
+
+def reference_measure(args) -> dict:
+    variant = "gol_ref_noprintf" if args.ref_variant == "noprintf" else "gol_ref"
+    exe = os.path.join(ROOT, "baseline", "_ref", "bin", variant)
+    mpirun = os.path.join(ROOT, "baseline", "_ref", "bin", "mpirun")
+    if not (os.path.exists(exe) and os.path.exists(mpirun)):
+        return {"impl": "reference", "unavailable": "baseline/_ref/bin is missing: run baseline/build_ref.sh "
+                "(pip cannot install the reference: it has no setup.py/pyproject.toml)"}
+    gens = args.ref_gens
+    n = args.gpus
+
+    def run(iters: int) -> float:
+        # stdout carries the device-printf flood (gol-with-cuda.cu:223): keep only the tail
+        cmd = [mpirun, "-n", str(n), exe, "1", str(SIZE), str(iters), "512", "0"]
+        import tempfile
+
+        with tempfile.TemporaryFile() as fo:
+            p = subprocess.run(cmd, stdout=fo, stderr=subprocess.PIPE)
+            size = fo.tell() if fo.tell() else os.fstat(fo.fileno()).st_size
+            fo.seek(max(0, size - (1 << 16)))
+            tail = fo.read()
+        if p.returncode != 0:
+            raise RuntimeError(f"reference exited {p.returncode}: {p.stderr[-500:]!r}")
+        m = re.search(rb"TOTAL DURATION : ([0-9.]+), number of cell updates = (\d+)", tail)
+        if not m:
+            raise RuntimeError("reference printed no TOTAL DURATION line")
+        return float(m.group(1))
+
+    from gol_b200.utils.clocks import ClockSampler
+
+    try:
+        for _ in range(min(args.warmup, 1)):
+            run(max(1, gens // 4))                      # warm-up: one short untimed run
+        sampler = ClockSampler(period_ms=100).start()
+        total_s = 0.0
+        t0 = time.time()
+        for _ in range(args.steps):
+            total_s += run(gens)                        # the reference's own timer (gol-main.c:82,122)
+        wall = time.time() - t0
+        clocks = sampler.stop()
+    except Exception as e:  # noqa: BLE001
+        return {"impl": "reference", "unavailable": f"reference run failed: {e}"}
+    updates = float(n) * SIZE * SIZE * gens * args.steps
+    value = updates / total_s * 1e-9
+    e2e = updates / wall * 1e-9
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": n,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "uint8 cells",
+        "data": "synthetic (pattern 1, all ones: the reference has no random pattern; its per-cell work is data-independent)",
+        "config": {"model": "conway-life-torus", "cells_per_gpu": f"{SIZE}x{SIZE}", "generations_per_step": gens,
+                   "parallelism": f"row-slab ring x{n} (minimpi shared-memory MPI, baseline tooling)",
+                   "variant": args.ref_variant, "timer": "reference's own MPI_Wtime TOTAL DURATION",
+                   "l2": "working set 2 x 256 MiB per GPU > L2"},
+        "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")},
+        "e2e": {"value": e2e, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "note": "wall clock around the whole reference process incl. init (managed memory, no explicit copies)"},
+        "gpu_launches": gens * args.steps * n,
+    }
+
+
+# ---------------------------------------------------------------------------- our arm
+def run_ours(args) -> int:
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local_rank = env_rank()
+    if args.gpus > 1 and world != args.gpus:
+        # single-process launch for N > 1: re-exec under torchrun so that it is one rank per GPU
+        import socket
+
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    torch.cuda.set_device(local_rank)
+    distributed = world > 1
+    if distributed:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import gol_b200
+    from gol_b200 import Life
+    from gol_b200 import _native as nat
+    from gol_b200.utils.clocks import ClockSampler
+    from gol_b200.utils.timing import flush_l2
+
+    gens = args.gens
+    life = Life(args.size, args.size, mode=args.mode, k=args.k, depth=args.depth, threads=args.threads,
+                distributed=distributed)
+    life.world.set_stream(0, torch.cuda.current_stream().cuda_stream)
+    life.init(6, seed=1234, density=0.5).sync()
+    plan = life.plan
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # pinned host copy of the initial world for the end-to-end arm
+    stride = life.world.stride
+    host_words = torch.empty((args.size, stride), dtype=torch.int64).pin_memory()
+    nat.check(nat.lib.gol_world_read_packed(life.world._h, 0, host_words.data_ptr()))
+    host_pop = torch.zeros(1, dtype=torch.int64).pin_memory()
+
+    sampler = ClockSampler(gpu_index=local_rank, period_ms=50).start() if rank == 0 else None
+
+    for _ in range(args.warmup):
+        life.step(gens)
+    barrier()
+
+    # ---- kernel-only: K steps, CUDA events on the launching stream, L2 flushed between steps
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    launches0 = gol_b200.launch_count()
+    t_region0 = time.time()
+    for i in range(args.steps):
+        flush_l2()
+        barrier()
+        ev0[i].record()
+        life.step(gens)
+        ev1[i].record()
+    barrier()
+    life.sync()
+    launches = gol_b200.launch_count() - launches0
+    total_ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
+
+    # ---- end to end through the public API: H2D of the step's input, step, D2H of its result
+    for _ in range(min(args.warmup, 2)):
+        life.run_from_host(host_words, gens, host_pop)
+    barrier()
+    t0 = time.perf_counter()
+    pops = []
+    for i in range(args.steps):
+        life.run_from_host(host_words, gens, host_pop)
+        life.sync()                       # the result is needed on the host every step
+        pops.append(int(host_pop.item()))
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t_region1 = time.time()
+    clocks = sampler.stop() if sampler else {}
+
+    t = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if distributed:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+    updates = float(world) * args.size * args.size * gens * args.steps
+    value = updates / (total_ms * 1e-3) * 1e-9
+    e2e_value = updates / (e2e_ms * 1e-3) * 1e-9
+
+    if rank == 0:
+        from gol_b200.utils.metrics import measured_peaks
+
+        peaks = measured_peaks(ROOT)
+        per_gpu_cells = value * 1e9 / world
+        out = {
+            "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "1-bit cells (uint64 x64 packed)",
+            "data": "synthetic (random 50% density, counter-based hash, seed 1234)",
+            "config": {"model": "conway-life-torus", "cells_per_gpu": f"{args.size}x{args.size}",
+                       "generations_per_step": gens, "global_batch": world * args.size * args.size,
+                       "parallelism": f"row-slab ring x{world}, one process per GPU, NVLink P2P halo fused in kernel",
+                       "mode": plan["mode_name"], "k": plan["temporal_k"], "exchange_depth": plan["exchange_depth"],
+                       "threads_per_block": plan["threads_per_block"], "strip_rows": plan["strip_rows"],
+                       "l2": "L2 flushed (256 MiB write) before every timed step; within a step the 64 MiB "
+                             "double buffer is L2-resident by design"},
+            "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples")},
+            "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": int(host_words.numel() * 8),
+                    "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps,
+                    "api": "Life.run_from_host(pinned_words, generations, pinned_result); Life.sync()"},
+            "gpu_launches": int(launches),
+            "impl": "ours",
+            "roofline": {"per_gpu_tcells_per_s": per_gpu_cells * 1e-12,
+                         "hbm_single_pass_bound_tcells_per_s": peaks["hbm_gbs"] * 1e9 / 0.25 * 1e-12,
+                         "hbm_of": peaks.get("source")},
+            "population_after_step": pops[-1] if pops else None,
+        }
+        print(json.dumps(out), flush=True)
+    life.close()
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=SIZE)
+    ap.add_argument("--gens", type=int, default=GENS_PER_STEP)
+    ap.add_argument("--mode", default="auto")
+    ap.add_argument("--k", type=int, default=0)
+    ap.add_argument("--depth", type=int, default=0)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--ref-gens", type=int, default=int(os.environ.get("GOL_REF_GENS", "8")),
+                    help="generations per reference step (as shipped the reference prints from every cell; "
+                         "1024 generations would take minutes per step)")
+    ap.add_argument("--ref-variant", default=os.environ.get("GOL_REF_VARIANT", "as-shipped"),
+                    choices=["as-shipped", "noprintf"])
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -127,6 +127,15 @@ class Life:
             ms = float(t.item())
         return ms
 
+    def run_from_host(self, pinned_words, generations: int, pinned_result, local: int = 0) -> None:
+        """End-to-end step as a user would issue it: upload a packed world from pinned host
+        memory, advance it, and queue the population read-back into ``pinned_result`` (one
+        uint64 of pinned host memory).  Asynchronous; call :meth:`sync` before reading."""
+        self.world.load_packed(local, pinned_words, asynchronous=True)
+        self.world.step(generations)
+        self.world.population_async(local, pinned_result)
+        self.generation += generations
+
     # ---------------------------------------------------------------- metrics
     def population(self, global_sum: bool = True) -> int:
         n = sum(self.world.population(i) for i in range(self.world.nlocal))
