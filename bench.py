@@ -142,7 +142,9 @@ def run_ours(args) -> int:
     gens = args.gens
     life = Life(args.size, args.size, mode=args.mode, k=args.k, depth=args.depth, threads=args.threads,
                 distributed=distributed)
-    life.world.set_stream(0, torch.cuda.current_stream().cuda_stream)
+    stream = torch.cuda.Stream()          # a capturable (non-legacy) stream shared by torch and the core
+    torch.cuda.set_stream(stream)
+    life.world.set_stream(0, stream.cuda_stream)
     life.init(6, seed=1234, density=0.5).sync()
     plan = life.plan
 

@@ -105,136 +105,181 @@ __device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long l
   return c;
 }
 
-// x-neighbour words of `c` inside a warp row: bit j of L is the cell left of
-// bit j of c, the carry bit comes from the lane to the left.
-__device__ __forceinline__ void lane_neighbours(uint64_t c, uint64_t& L, uint64_t& R) {
-  const uint32_t lo = (uint32_t)c, hi = (uint32_t)(c >> 32);
-  const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);
-  const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);
-  const uint32_t Llo = __funnelshift_l(lhi, lo, 1), Lhi = __funnelshift_l(lo, hi, 1);
-  const uint32_t Rlo = __funnelshift_r(lo, hi, 1), Rhi = __funnelshift_r(hi, rlo, 1);
-  L = ((uint64_t)Lhi << 32) | Llo;
-  R = ((uint64_t)Rhi << 32) | Rlo;
+// ---- the bit-sliced generation stage, spelled out in 32-bit LOP3s -----------------------------
+// Each lane owns one 64-cell word as two 32-bit halves.  Per half and per generation:
+//   2 SHF (funnel shifts bring in the x-neighbour bit, across lanes via SHFL)
+//   2 LOP3 horizontal sum, 4 LOP3 vertical carry-save, 4 LOP3 rule decode  = 10 LOP3
+// The LUTs are written out so that ptxas cannot pick a longer decomposition.
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+  return r;
 }
 
-struct Stage {
-  HSum<uint64_t> a, b;  // horizontal sums of the two previous rows
-  uint64_t c;           // centre word of the previous row
+struct Half {
+  uint32_t a0, a1;  // horizontal sum planes of row r-2
+  uint32_t b0, b1;  // horizontal sum planes of row r-1
+  uint32_t c;       // centre cells of row r-1
 };
+struct Stage {
+  Half lo, hi;
+};
+
+// Feed the horizontal sum (h0,h1) and centre x of the newest row; returns the next
+// generation of the previous row and rotates the window.
+__device__ __forceinline__ uint32_t stage_half(Half& s, uint32_t h0, uint32_t h1, uint32_t x) {
+  const uint32_t t0 = lop3<0x96>(s.a0, s.b0, h0);   // weight 1
+  const uint32_t k0 = lop3<0xE8>(s.a0, s.b0, h0);   // weight 2
+  const uint32_t t1 = lop3<0x96>(s.a1, s.b1, h1);   // weight 2
+  const uint32_t k1 = lop3<0xE8>(s.a1, s.b1, h1);   // weight 4
+  // 3x3 total (centre included) = t0 + 2(k0 + t1) + 4 k1;  next = total==3 | centre & total==4
+  const uint32_t e3 = lop3<0x14>(k0, t1, k1);       // (k0^t1) & ~k1        -> total in {2,3}
+  const uint32_t e4 = lop3<0x42>(k0, t1, k1);       // ~(k0^t1) & (k1^k0)   -> total in {4,5}
+  const uint32_t v = lop3<0x08>(t0, s.c, e4);       // ~t0 & centre & e4    -> centre & total==4
+  const uint32_t o = lop3<0xEA>(t0, e3, v);         // (t0 & e3) | v
+  s.a0 = s.b0;
+  s.a1 = s.b1;
+  s.b0 = h0;
+  s.b1 = h1;
+  s.c = x;
+  return o;
+}
 
 // Push one row through K generation stages.  Fed rows y_in+0, y_in+1, ... the
 // value returned at step i (i >= 2K) is generation +K of row y_in + i - K.
 template <int K>
-__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x) {
+__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64) {
+  uint32_t lo = (uint32_t)x64, hi = (uint32_t)(x64 >> 32);
 #pragma unroll
   for (int t = 0; t < K; ++t) {
-    uint64_t L, R;
-    lane_neighbours(x, L, R);
-    const HSum<uint64_t> h = hsum3(L, x, R);
-    const uint64_t o = life_rule(s[t].a, s[t].b, h, s[t].c);
-    s[t].a = s[t].b;
-    s[t].b = h;
-    s[t].c = x;
-    x = o;
+    const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);    // left lane's top half: carries bit 63
+    const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);  // right lane's low half: carries bit 0
+    const uint32_t Llo = __funnelshift_l(lhi, lo, 1), Lhi = __funnelshift_l(lo, hi, 1);
+    const uint32_t Rlo = __funnelshift_r(lo, hi, 1), Rhi = __funnelshift_r(hi, rlo, 1);
+    const uint32_t h0lo = lop3<0x96>(Llo, lo, Rlo), h1lo = lop3<0xE8>(Llo, lo, Rlo);
+    const uint32_t h0hi = lop3<0x96>(Lhi, hi, Rhi), h1hi = lop3<0xE8>(Lhi, hi, Rhi);
+    const uint32_t olo = stage_half(s[t].lo, h0lo, h1lo, lo);
+    const uint32_t ohi = stage_half(s[t].hi, h0hi, h1hi, hi);
+    lo = olo;
+    hi = ohi;
   }
-  return x;
+  return ((uint64_t)hi << 32) | lo;
+}
+
+// Geometry of one warp task, shared by the EDGE / interior instantiations of the row loop.
+struct TaskGeom {
+  int64_t y0, y1;   // output rows [y0, y1)
+  int64_t wi;       // my word column
+  bool owner;       // lanes 1..30 inside the row own output words
+};
+
+// Stream rows [y0-K, y1+K) through the K stages and store rows [y0, y1).  EDGE = the strip
+// touches freshly exchanged halo rows (recv buffers) instead of in-slab rows.
+template <int K, bool EDGE>
+__device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g) {
+  constexpr int B = ((2 * K) % 4 == 0) ? 4 : 2;  // rows per batch; 2K is a multiple of B
+  const int64_t y_in = g.y0 - K;
+  const int n_in = (int)(g.y1 - g.y0) + 2 * K;
+  const int last = n_in - 1;
+  const int nb = (n_in + B - 1) / B;
+  const uint64_t* in_col = c.in + g.wi;
+  const uint64_t* top_col = c.rtop + g.wi + (int64_t)c.ext_in * c.stride;  // row y (<0) at top_col + y*stride
+  const uint64_t* bot_col = c.rbot + g.wi - c.H * c.stride;                // row y (>=H) at bot_col + y*stride
+  uint64_t* out_col = c.out + g.wi;
+
+  auto load_row = [&](int i) -> uint64_t {
+    i = i < last ? i : last;  // rows past the end are re-reads of the last row (never stored)
+    const int64_t y = y_in + i;
+    const uint64_t* p = in_col + y * c.stride;
+    if (EDGE) {
+      p = (y < 0) ? top_col + y * c.stride : p;
+      p = (y >= c.H) ? bot_col + y * c.stride : p;
+    }
+    return ld_cg(p);
+  };
+
+  Stage s[K];
+#pragma unroll
+  for (int t = 0; t < K; ++t) {
+    s[t].lo.a0 = s[t].lo.a1 = s[t].lo.b0 = s[t].lo.b1 = s[t].lo.c = 0;
+    s[t].hi.a0 = s[t].hi.a1 = s[t].hi.b0 = s[t].hi.b1 = s[t].hi.c = 0;
+  }
+
+  uint64_t nxt[B];
+#pragma unroll
+  for (int j = 0; j < B; ++j) nxt[j] = load_row(j);
+
+  for (int b = 0; b < nb; ++b) {
+    uint64_t cur[B];
+#pragma unroll
+    for (int j = 0; j < B; ++j) cur[j] = nxt[j];
+#pragma unroll
+    for (int j = 0; j < B; ++j) nxt[j] = load_row((b + 1) * B + j);
+    const int64_t yb = y_in + (int64_t)b * B - K;  // output row of the batch's first input row
+    const bool warm = b * B >= 2 * K;              // whole batches: 2K % B == 0
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const uint64_t o = push_row<K>(s, cur[j]);
+      const int64_t y = yb + j;
+      if (warm && g.owner && y < g.y1) st_cg(out_col + y * c.stride, o);
+    }
+  }
 }
 
 // One warp task of a fused pass: strip `strip` of column group `cg`.
 template <int K>
 __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int strip_rows,
                                            int strip, int cg, int lane) {
-  constexpr int B = 4;  // rows per load batch (software prefetch depth)
   const int ext_out = c.ext_in - K;
-  const int64_t y_first = -(int64_t)ext_out;
-  const int64_t y_end_all = c.H + ext_out;
-  const int64_t y0 = y_first + (int64_t)strip * strip_rows;
-  int64_t y1 = y0 + strip_rows;
-  if (y1 > y_end_all) y1 = y_end_all;
+  TaskGeom g;
+  g.y0 = -(int64_t)ext_out + (int64_t)strip * strip_rows;
+  g.y1 = g.y0 + strip_rows;
+  if (g.y1 > c.H + ext_out) g.y1 = c.H + ext_out;
 
   // my word column (torus wrap in x, also when the row has < 32 words)
   int64_t wi = (int64_t)cg * kValidLanes - 1 + lane;
   wi %= c.ws;
   if (wi < 0) wi += c.ws;
-  const bool owner = lane >= 1 && lane <= kValidLanes && ((int64_t)cg * kValidLanes + lane - 1) < c.ws;
+  g.wi = wi;
+  g.owner = lane >= 1 && lane <= kValidLanes && ((int64_t)cg * kValidLanes + lane - 1) < c.ws;
 
-  const bool reads_top = c.consume && (y0 - K < 0);
-  const bool reads_bot = c.consume && (y1 + K > c.H);
+  const bool reads_top = c.consume && (g.y0 - K < 0);
+  const bool reads_bot = c.consume && (g.y1 + K > c.H);
   if (reads_top || reads_bot) {
     if (lane == 0) {
       if (reads_top) wait_words(st, 0, c.target);
       if (reads_bot) wait_words(st, 1, c.target);
     }
     __syncwarp();
+    stream_rows<K, true>(c, g);
+  } else {
+    stream_rows<K, false>(c, g);
   }
 
-  const int64_t y_in = y0 - K;
-  const int n_in = (int)(y1 - y0) + 2 * K;
-  const uint64_t* in_col = c.in + wi;
-  const uint64_t* top_col = c.rtop + wi + (int64_t)c.ext_in * c.stride;  // row y at top_col + y*stride (y<0)
-  const uint64_t* bot_col = c.rbot + wi - c.H * c.stride;                // row y at bot_col + y*stride (y>=H)
-  const bool fresh = c.consume != 0;
-
-  auto load_row = [&](int64_t y) -> uint64_t {
-    if (fresh && y < 0) return ld_cg(top_col + y * c.stride);
-    if (fresh && y >= c.H) return ld_cg(bot_col + y * c.stride);
-    return in_col[y * c.stride];
-  };
-
-  Stage s[K];
-#pragma unroll
-  for (int t = 0; t < K; ++t) {
-    s[t].a.s0 = s[t].a.s1 = s[t].b.s0 = s[t].b.s1 = s[t].c = 0;
-  }
-
-  uint64_t* out_col = c.out + wi;
-  const int64_t push_lo = c.push;            // rows [0, push) go to prev
-  const int64_t push_hi = c.H - c.push;      // rows [H-push, H) go to next
-  int rows_top = 0, rows_bot = 0;
-
-  uint64_t nxt[B];
-#pragma unroll
-  for (int j = 0; j < B; ++j) nxt[j] = (j < n_in) ? load_row(y_in + j) : 0ull;
-
-  for (int i0 = 0; i0 < n_in; i0 += B) {
-    uint64_t cur[B];
-#pragma unroll
-    for (int j = 0; j < B; ++j) cur[j] = nxt[j];
-#pragma unroll
-    for (int j = 0; j < B; ++j) {
-      const int i = i0 + B + j;
-      nxt[j] = (i < n_in) ? load_row(y_in + i) : 0ull;
-    }
-#pragma unroll
-    for (int j = 0; j < B; ++j) {
-      const int i = i0 + j;
-      if (i < n_in) {
-        const uint64_t o = push_row<K>(s, cur[j]);
-        if (i >= 2 * K) {
-          const int64_t y = y_in + i - K;
-          if (owner) st_cg(out_col + y * c.stride, o);
-          if (c.push) {
-            if (y >= 0 && y < push_lo) {
-              if (owner) st_cg(c.ptop + y * c.stride + wi, o);
-              ++rows_top;
-            }
-            if (y >= push_hi && y < c.H) {
-              if (owner) st_cg(c.pbot + (y - push_hi) * c.stride + wi, o);
-              ++rows_bot;
-            }
-          }
-        }
+  // Halo push (fused MPI_Isend, gol-main.c:104-107): the rows this task just produced that the
+  // ring neighbours need go straight into their recv buffers, then the word count is published.
+  if (c.push) {
+    const int64_t t0 = g.y0 > 0 ? g.y0 : 0;
+    const int64_t t1 = g.y1 < c.push ? g.y1 : c.push;              // rows [0, push) -> prev
+    const int64_t b0 = g.y0 > c.H - c.push ? g.y0 : c.H - c.push;  // rows [H-push, H) -> next
+    const int64_t b1 = g.y1 < c.H ? g.y1 : c.H;
+    const int rows_top = t1 > t0 ? (int)(t1 - t0) : 0;
+    const int rows_bot = b1 > b0 ? (int)(b1 - b0) : 0;
+    if (rows_top | rows_bot) {
+      if (g.owner) {
+        const uint64_t* mine = c.out + wi;
+        for (int64_t y = t0; y < t1; ++y) st_cg(c.ptop + y * c.stride + wi, ld_cg(mine + y * c.stride));
+        for (int64_t y = b0; y < b1; ++y)
+          st_cg(c.pbot + (y - (c.H - c.push)) * c.stride + wi, ld_cg(mine + y * c.stride));
       }
-    }
-  }
-
-  if (rows_top | rows_bot) {
-    __threadfence_system();
-    __syncwarp();
-    const unsigned owners = __popc(__ballot_sync(kFull, owner));
-    if (lane == 0) {
-      if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
-      if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
+      __threadfence_system();
+      __syncwarp();
+      const unsigned owners = __popc(__ballot_sync(kFull, g.owner));
+      if (lane == 0) {
+        if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
+        if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
+      }
     }
   }
 }

@@ -787,7 +787,48 @@ int gol_world_population(gol_world_t* w, int li, uint64_t* out) {
   return GOL_OK;
 }
 
-static int step_cuda(gol_world* w, int64_t gens) {
+static bool graph_capable(const Group& g) {
+  // the legacy default stream cannot be captured
+  return g.stream != nullptr && g.stream != cudaStreamLegacy && g.stream != cudaStreamPerThread;
+}
+
+// CUDA graph of the whole pass schedule for `gens` generations on one device (cached).
+static int get_graph(gol_world* w, Group& g, int64_t gens, const std::vector<PassItem>& items,
+                     std::pair<cudaGraphExec_t, int>** out) {
+  auto it = g.graphs.find(gens);
+  if (it == g.graphs.end()) {
+    const uint64_t before = launch_count_value();
+    cudaGraph_t graph = nullptr;
+    CU_TRY(cudaStreamBeginCapture(g.stream, cudaStreamCaptureModeThreadLocal));
+    int rc = GOL_OK;
+    for (auto& item : items) {
+      rc = launch_item(w, g, item);
+      if (rc) break;
+    }
+    cudaError_t e = cudaStreamEndCapture(g.stream, &graph);
+    count_launch(before - launch_count_value());  // capture is not execution
+    if (rc) {
+      if (graph) cudaGraphDestroy(graph);
+      return rc;
+    }
+    if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph instantiate failed: %s", cudaGetErrorString(e));
+    if (g.graphs.size() > 16) {
+      for (auto& kv : g.graphs) cudaGraphExecDestroy(kv.second.first);
+      g.graphs.clear();
+    }
+    it = g.graphs.emplace(gens, std::make_pair(exec, (int)items.size())).first;
+  }
+  *out = &it->second;
+  return GOL_OK;
+}
+
+// launch = false only builds (and caches) the CUDA graphs so that a timed step does not
+// include capture / instantiation.
+static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
   const gol_plan_t& pl = w->plan;
   const bool use_graph = !(w->cfg.flags & GOL_FLAG_NO_GRAPH);
   int64_t todo = gens;
@@ -795,7 +836,9 @@ static int step_cuda(gol_world* w, int64_t gens) {
   if (pl.mode == GOL_MODE_PERSISTENT) {
     const int P = pl.exchange_depth / pl.temporal_k;
     const int64_t periods = todo / pl.exchange_depth;
-    if (periods > 0) {
+    if (periods > 0 && !launch) {
+      todo -= periods * pl.exchange_depth;
+    } else if (periods > 0) {
       const int64_t max_periods = (int64_t)(1 << 20);
       int64_t left = periods;
       while (left > 0) {
@@ -836,37 +879,24 @@ static int step_cuda(gol_world* w, int64_t gens) {
   if (use_graph && items.size() > 2) {
     for (auto& g : w->groups) {
       CU_TRY(cudaSetDevice(g.device));
-      auto it = g.graphs.find(todo);
-      if (it == g.graphs.end()) {
-        const uint64_t before = launch_count_value();
-        cudaGraph_t graph = nullptr;
-        CU_TRY(cudaStreamBeginCapture(g.stream, cudaStreamCaptureModeThreadLocal));
-        int rc = GOL_OK;
-        for (auto& item : items) {
-          rc = launch_item(w, g, item);
-          if (rc) break;
-        }
-        cudaError_t e = cudaStreamEndCapture(g.stream, &graph);
-        count_launch(before - launch_count_value());  // capture is not execution
-        if (rc) {
-          if (graph) cudaGraphDestroy(graph);
-          return rc;
-        }
-        if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
-        cudaGraphExec_t exec = nullptr;
-        e = cudaGraphInstantiate(&exec, graph, 0);
-        cudaGraphDestroy(graph);
-        if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "graph instantiate failed: %s", cudaGetErrorString(e));
-        if (g.graphs.size() > 16) {
-          for (auto& kv : g.graphs) cudaGraphExecDestroy(kv.second.first);
-          g.graphs.clear();
-        }
-        it = g.graphs.emplace(todo, std::make_pair(exec, (int)items.size())).first;
+      if (!graph_capable(g)) {
+        if (launch)
+          for (auto& item : items) {
+            int rc = launch_item(w, g, item);
+            if (rc) return rc;
+          }
+        continue;
       }
-      CU_TRY(cudaGraphLaunch(it->second.first, g.stream));
-      count_launch((uint64_t)it->second.second);
+      std::pair<cudaGraphExec_t, int>* ge = nullptr;
+      int rc = get_graph(w, g, todo, items, &ge);
+      if (rc) return rc;
+      if (!launch) continue;
+      CU_TRY(cudaGraphLaunch(ge->first, g.stream));
+      count_launch((uint64_t)ge->second);
     }
+    if (!launch) return GOL_OK;
   } else {
+    if (!launch) return GOL_OK;
     for (auto& item : items)
       for (auto& g : w->groups) {
         CU_TRY(cudaSetDevice(g.device));
@@ -932,11 +962,14 @@ int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms) {
     for (size_t i = 0; i < w->slabs.size(); ++i) ms[i] = t;
     return rc;
   }
+  if (!w->connected) return set_error(GOL_ERR_STATE, "gol_world_connect has not been called");
+  int rc = step_cuda(w, gens, /*launch=*/false);  // graphs built outside the timed region
+  if (rc) return rc;
   for (auto& g : w->groups) {
     CU_TRY(cudaSetDevice(g.device));
     CU_TRY(cudaEventRecord(g.e0, g.stream));
   }
-  int rc = gol_world_step(w, gens);
+  rc = gol_world_step(w, gens);
   if (rc) return rc;
   for (auto& g : w->groups) {
     CU_TRY(cudaSetDevice(g.device));
