@@ -68,6 +68,7 @@ struct PassParams {
   int32_t col_groups; // warp tasks per strip
   int32_t nstrips;
   int32_t pad;
+  uint32_t mul2, mul31;  // 2 and 2^31, passed as data so the shift-by-multiply variant keeps its IMADs
 };
 
 }  // namespace gol

@@ -15,7 +15,7 @@
 // (NVLink P2P or CUDA-IPC) pointer and publish a word count with
 // red.release.sys; the warps that need a fresh halo spin on ld.acquire.sys.
 // Those warps are scheduled first (lowest task ids).
-#include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "kernels.cuh"
 
@@ -81,12 +81,16 @@ struct PassCtx {
   unsigned long long target;
   int64_t H, ws, stride;
   int ext_in, consume, push;
+  uint32_t m2, m31;       // 2 and 2^31 as run-time values (shift-by-multiply variant)
 };
 
 __device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long long pass,
                                             unsigned long long exch, unsigned long long words_seen,
-                                            int ext_in, int consume, int push) {
+                                            int ext_in, int consume, int push,
+                                            uint32_t m2 = 2u, uint32_t m31 = 0x80000000u) {
   PassCtx c;
+  c.m2 = m2;
+  c.m31 = m31;
   const int64_t stride = st->stride;
   c.in = st->buf[pass & 1] + (int64_t)st->G * stride;
   c.out = st->buf[(pass + 1) & 1] + (int64_t)st->G * stride;
@@ -115,6 +119,15 @@ __device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
   uint32_t r;
   asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
   return r;
+}
+
+// a * b + {c_hi:c_lo} as one IMAD.WIDE (the 64-bit addend rides along for free)
+__device__ __forceinline__ uint64_t mad_wide(uint32_t a, uint32_t b, uint32_t c_lo, uint32_t c_hi) {
+  uint64_t d;
+  asm("{\n\t.reg .b64 c;\n\tmov.b64 c, {%3, %4};\n\tmad.wide.u32 %0, %1, %2, c;\n\t}"
+      : "=l"(d)
+      : "r"(a), "r"(b), "r"(c_lo), "r"(c_hi));
+  return d;
 }
 
 struct Half {
@@ -146,23 +159,49 @@ __device__ __forceinline__ uint32_t stage_half(Half& s, uint32_t h0, uint32_t h1
   return o;
 }
 
-// Push one row through K generation stages.  Fed rows y_in+0, y_in+1, ... the
-// value returned at step i (i >= 2K) is generation +K of row y_in + i - K.
-template <int K>
-__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64) {
+// Push one row through generation stages [0, nst).  Fed rows y_in+0, y_in+1, ... the value
+// returned at step i (i >= 2K, nst == K) is generation +K of row y_in + i - K.  nst < K is used
+// while the pipeline fills: stage t has no valid input before step 2t, so running it is waste.
+//
+// V selects how the x-neighbour words are formed:
+//   V = 0  funnel shifts (SHF, ALU pipe): 4 per word
+//   V = 1  integer multiply-adds (IMAD / IMAD.WIDE / IMAD.HI, FMA pipe) by 2 and 2^31 held in
+//          registers, which moves the shifts off the pipe that the LOP3s saturate
+template <int K, int V>
+__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64, int nst, uint32_t m2,
+                                             uint32_t m31) {
   uint32_t lo = (uint32_t)x64, hi = (uint32_t)(x64 >> 32);
 #pragma unroll
   for (int t = 0; t < K; ++t) {
-    const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);    // left lane's top half: carries bit 63
-    const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);  // right lane's low half: carries bit 0
-    const uint32_t Llo = __funnelshift_l(lhi, lo, 1), Lhi = __funnelshift_l(lo, hi, 1);
-    const uint32_t Rlo = __funnelshift_r(lo, hi, 1), Rhi = __funnelshift_r(hi, rlo, 1);
-    const uint32_t h0lo = lop3<0x96>(Llo, lo, Rlo), h1lo = lop3<0xE8>(Llo, lo, Rlo);
-    const uint32_t h0hi = lop3<0x96>(Lhi, hi, Rhi), h1hi = lop3<0xE8>(Lhi, hi, Rhi);
-    const uint32_t olo = stage_half(s[t].lo, h0lo, h1lo, lo);
-    const uint32_t ohi = stage_half(s[t].hi, h0hi, h1hi, hi);
-    lo = olo;
-    hi = ohi;
+    if (t < nst) {
+      uint32_t Llo, Lhi, Rlo, Rhi;
+      if (V == 0) {
+        const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);    // left lane's top half: carries bit 63
+        const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);  // right lane's low half: carries bit 0
+        Llo = __funnelshift_l(lhi, lo, 1);
+        Lhi = __funnelshift_l(lo, hi, 1);
+        Rlo = __funnelshift_r(lo, hi, 1);
+        Rhi = __funnelshift_r(hi, rlo, 1);
+      } else {
+        // sender side: my bit 63 as a 0/1 value, my bit 0 moved to bit 31
+        const uint32_t cin = __shfl_up_sync(kFull, __umulhi(hi, m2), 1);
+        const uint32_t rin = __shfl_down_sync(kFull, lo * m31, 1);
+        // {hi:lo} * 2 + carry-in: lo*2 is 33 bits wide, its bit 32 lands in the high word
+        const uint64_t L = mad_wide(lo, m2, cin, hi * m2);
+        // {hi:lo} / 2 + carry-in: hi * 2^31 = {hi >> 1 : hi << 31}
+        const uint64_t R = mad_wide(hi, m31, __umulhi(lo, m31), rin);
+        Llo = (uint32_t)L;
+        Lhi = (uint32_t)(L >> 32);
+        Rlo = (uint32_t)R;
+        Rhi = (uint32_t)(R >> 32);
+      }
+      const uint32_t h0lo = lop3<0x96>(Llo, lo, Rlo), h1lo = lop3<0xE8>(Llo, lo, Rlo);
+      const uint32_t h0hi = lop3<0x96>(Lhi, hi, Rhi), h1hi = lop3<0xE8>(Lhi, hi, Rhi);
+      const uint32_t olo = stage_half(s[t].lo, h0lo, h1lo, lo);
+      const uint32_t ohi = stage_half(s[t].hi, h0hi, h1hi, hi);
+      lo = olo;
+      hi = ohi;
+    }
   }
   return ((uint64_t)hi << 32) | lo;
 }
@@ -176,17 +215,17 @@ struct TaskGeom {
 
 // Stream rows [y0-K, y1+K) through the K stages and store rows [y0, y1).  EDGE = the strip
 // touches freshly exchanged halo rows (recv buffers) instead of in-slab rows.
-template <int K, bool EDGE>
+template <int K, int V, bool EDGE>
 __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g) {
-  constexpr int B = ((2 * K) % 4 == 0) ? 4 : 2;  // rows per batch; 2K is a multiple of B
+  constexpr int B = 4;  // rows per batch (software prefetch depth)
   const int64_t y_in = g.y0 - K;
   const int n_in = (int)(g.y1 - g.y0) + 2 * K;
   const int last = n_in - 1;
-  const int nb = (n_in + B - 1) / B;
   const uint64_t* in_col = c.in + g.wi;
   const uint64_t* top_col = c.rtop + g.wi + (int64_t)c.ext_in * c.stride;  // row y (<0) at top_col + y*stride
   const uint64_t* bot_col = c.rbot + g.wi - c.H * c.stride;                // row y (>=H) at bot_col + y*stride
   uint64_t* out_col = c.out + g.wi;
+  const uint32_t m2 = c.m2, m31 = c.m31;
 
   auto load_row = [&](int i) -> uint64_t {
     i = i < last ? i : last;  // rows past the end are re-reads of the last row (never stored)
@@ -206,29 +245,41 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
     s[t].hi.a0 = s[t].hi.a1 = s[t].hi.b0 = s[t].hi.b1 = s[t].hi.c = 0;
   }
 
+  // pipeline fill: the first 2K rows produce no output; row i only feeds stages 0..i/2
+  if (K <= 4) {
+    uint64_t pre[2 * K];
+#pragma unroll
+    for (int i = 0; i < 2 * K; ++i) pre[i] = load_row(i);
+#pragma unroll
+    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, pre[i], (i / 2 + 1 < K) ? i / 2 + 1 : K, m2, m31);
+  } else {
+    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, load_row(i), K, m2, m31);
+  }
+
+  // steady state: every row in yields one row out
+  const int n_main = n_in - 2 * K;
+  const int nb = (n_main + B - 1) / B;
   uint64_t nxt[B];
 #pragma unroll
-  for (int j = 0; j < B; ++j) nxt[j] = load_row(j);
-
+  for (int j = 0; j < B; ++j) nxt[j] = load_row(2 * K + j);
   for (int b = 0; b < nb; ++b) {
     uint64_t cur[B];
 #pragma unroll
     for (int j = 0; j < B; ++j) cur[j] = nxt[j];
 #pragma unroll
-    for (int j = 0; j < B; ++j) nxt[j] = load_row((b + 1) * B + j);
-    const int64_t yb = y_in + (int64_t)b * B - K;  // output row of the batch's first input row
-    const bool warm = b * B >= 2 * K;              // whole batches: 2K % B == 0
+    for (int j = 0; j < B; ++j) nxt[j] = load_row(2 * K + (b + 1) * B + j);
+    const int64_t yb = g.y0 + (int64_t)b * B;
 #pragma unroll
     for (int j = 0; j < B; ++j) {
-      const uint64_t o = push_row<K>(s, cur[j]);
+      const uint64_t o = push_row<K, V>(s, cur[j], K, m2, m31);
       const int64_t y = yb + j;
-      if (warm && g.owner && y < g.y1) st_cg(out_col + y * c.stride, o);
+      if (g.owner && y < g.y1) st_cg(out_col + y * c.stride, o);
     }
   }
 }
 
 // One warp task of a fused pass: strip `strip` of column group `cg`.
-template <int K>
+template <int K, int V>
 __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int strip_rows,
                                            int strip, int cg, int lane) {
   const int ext_out = c.ext_in - K;
@@ -252,9 +303,9 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int 
       if (reads_bot) wait_words(st, 1, c.target);
     }
     __syncwarp();
-    stream_rows<K, true>(c, g);
+    stream_rows<K, V, true>(c, g);
   } else {
-    stream_rows<K, false>(c, g);
+    stream_rows<K, V, false>(c, g);
   }
 
   // Halo push (fused MPI_Isend, gol-main.c:104-107): the rows this task just produced that the
@@ -309,7 +360,7 @@ __device__ __forceinline__ void finish_pass(SlabState* st, const PassParams& p, 
   }
 }
 
-template <int K, int MAXT, int MINB>
+template <int K, int MAXT, int MINB, int V>
 __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* states, PassParams p) {
   SlabState* st = states + blockIdx.y;
   const int lane = threadIdx.x & 31;
@@ -317,10 +368,11 @@ __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* state
   const int task = blockIdx.x * wpb + (threadIdx.x >> 5);
   const int ntasks = p.nstrips * p.col_groups;
   if (task < ntasks) {
-    const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push);
+    const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push,
+                               p.mul2, p.mul31);
     const int order = task / p.col_groups;
     const int cg = task - order * p.col_groups;
-    fused_task<K>(st, c, p.strip_rows, strip_of_order(order, p.nstrips), cg, lane);
+    fused_task<K, V>(st, c, p.strip_rows, strip_of_order(order, p.nstrips), cg, lane);
   }
   finish_pass(st, p, gridDim.x);
 }
@@ -491,7 +543,7 @@ __global__ void __launch_bounds__(MAXT, MINB) life_persistent_kernel(SlabState* 
       for (int task = gwarp; task < ntasks; task += nwarps) {
         const int order = task / pp.pass.col_groups;
         const int cg = task - order * pp.pass.col_groups;
-        fused_task<K>(st, c, pp.pass.strip_rows, strip_of_order(order, nstrips), cg, lane);
+        fused_task<K, 0>(st, c, pp.pass.strip_rows, strip_of_order(order, nstrips), cg, lane);
       }
     }
     grid_barrier(pp.barrier, gridDim.x, epoch);
@@ -710,8 +762,8 @@ template <> struct FusedCfg<4> { static constexpr int kMaxT = 256, kMinB = 2; };
 template <> struct FusedCfg<6> { static constexpr int kMaxT = 128, kMinB = 3; };
 template <> struct FusedCfg<8> { static constexpr int kMaxT = 128, kMinB = 3; };
 
-template <int K> const void* fused_fn() {
-  return (const void*)&life_fused_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
+template <int K, int V = 0> const void* fused_fn() {
+  return (const void*)&life_fused_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB, V>;
 }
 template <int K> const void* persistent_fn() {
   return (const void*)&life_persistent_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
@@ -735,6 +787,16 @@ template <int K> const void* persistent_fn() {
 static uint64_t g_launches = 0;
 void count_launch(uint64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }
 uint64_t launch_count_value() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
+// GOL_FUSED_VARIANT=1 selects the shift-by-multiply instantiation (K = 4 only).
+static int fused_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GOL_FUSED_VARIANT");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
 
 bool fused_k_supported(int K) { return K == 1 || K == 2 || K == 3 || K == 4 || K == 6 || K == 8; }
 
@@ -774,11 +836,14 @@ cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParam
                          cudaStream_t s) {
   const void* fn = nullptr;
   GOL_DISPATCH_K(K, fn = fused_fn<KK>());
+  if (fused_variant() == 1 && K == 4) fn = fused_fn<4, 1>();
   if (!fn) return cudaErrorInvalidValue;
   const int wpb = threads / 32;
   const int ntasks = p.nstrips * p.col_groups;
   dim3 grid((unsigned)((ntasks + wpb - 1) / wpb), (unsigned)nslabs);
   PassParams pp = p;
+  pp.mul2 = 2u;
+  pp.mul31 = 0x80000000u;
   void* args[] = {(void*)&d_states, (void*)&pp};
   count_launch(1);
   return cudaLaunchKernel(fn, grid, dim3((unsigned)threads), args, 0, s);
