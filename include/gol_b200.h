@@ -178,6 +178,39 @@ int gol_cuda_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_
                        const uint64_t* d_bottom, int64_t W, int64_t H, int threads_per_block,
                        void* stream);
 
+/* ---- stepping without any allocation ---------------------------------------------
+ * (No counterpart in the reference: it allocates everything with cudaMallocManaged.)
+ *
+ * For callers that are not allowed to allocate device memory at the point where they need
+ * a step: a plug-in inside an application whose memory pool already owns the whole GPU, a
+ * latency-critical loop that must not take the driver's allocation lock, a component that
+ * runs after the host program has frozen its memory map.  Everything else in this header
+ * gets working memory from cudaMalloc (gol_world_create) or from the caller; this call
+ * uses a fixed scratch array of GOL_NOALLOC_SCRATCH_BYTES that is part of the library's
+ * device image.  Every GPU that loads the library carries that array until the process
+ * exits, whether or not the call is ever made.
+ *
+ * Advances a stand-alone packed W x H torus (row stride gol_row_stride_words(W), no ring
+ * neighbours) by `gens` generations.  d_a holds the input and is overwritten; d_b is a
+ * second buffer of the same size; *result_in_b tells which of the two holds the result
+ * (0: d_a, 1: d_b).  Work is enqueued on `stream` and is asynchronous like the other
+ * gol_cuda_* calls.  No cudaMalloc / cudaFree / allocating routine is called, now or later.
+ *
+ * Limits and rules:
+ *  - W <= GOL_NOALLOC_MAX_WIDTH, otherwise GOL_ERR_UNSUPPORTED (the halo rows of a wider
+ *    grid do not fit the scratch array); any H >= 1.
+ *  - The first call on each device looks up the scratch array's device address
+ *    (cudaGetSymbolAddress).  Make that first call outside any stream capture.
+ *  - All calls on one device share the one scratch array, and it keeps whatever the last
+ *    call left in it; each call re-initialises the counters and flags it needs.  Two calls
+ *    whose GPU work can overlap (different streams, no dependency) corrupt each other:
+ *    serialise them.
+ */
+#define GOL_NOALLOC_MAX_WIDTH 131072
+#define GOL_NOALLOC_SCRATCH_BYTES (272 * 1024)
+int gol_cuda_run_torus_noalloc(uint64_t* d_a, uint64_t* d_b, int64_t W, int64_t H, int64_t gens,
+                               int threads_per_block, void* stream, int* result_in_b);
+
 #ifdef __cplusplus
 }
 #endif
