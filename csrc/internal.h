@@ -67,8 +67,41 @@ struct PassParams {
   int32_t strip_rows; // output rows per warp task
   int32_t col_groups; // warp tasks per strip
   int32_t nstrips;
-  int32_t pad;
+  int32_t edge_rows;  // > 0: the first / last edge_rows output rows are strips of their own (scheduled
+                      // first and short, so the halo push leaves early and overlaps the interior)
   uint32_t mul2, mul31;  // 2 and 2^31, passed as data so the shift-by-multiply variant keeps its IMADs
 };
+
+// ---- strip decomposition of one pass (shared by host planner and kernels) ----------------
+// Output rows [first, end) are cut into warp tasks.  With edge_rows > 0 the two edge strips
+// come first in task order (order 0 = top, 1 = bottom), then the interior strips.
+GOL_HD int strip_count(int64_t rows_total, int strip_rows, int edge_rows) {
+  if (edge_rows > 0 && rows_total > 2 * (int64_t)edge_rows)
+    return 2 + (int)((rows_total - 2 * edge_rows + strip_rows - 1) / strip_rows);
+  return (int)((rows_total + strip_rows - 1) / strip_rows);
+}
+
+GOL_HD void strip_range(int order, int nstrips, int64_t first, int64_t end, int strip_rows, int edge_rows,
+                        int64_t* y0, int64_t* y1) {
+  if (edge_rows > 0 && end - first > 2 * (int64_t)edge_rows) {
+    if (order == 0) {
+      *y0 = first;
+      *y1 = first + edge_rows;
+    } else if (order == 1) {
+      *y0 = end - edge_rows;
+      *y1 = end;
+    } else {
+      *y0 = first + edge_rows + (int64_t)(order - 2) * strip_rows;
+      *y1 = *y0 + strip_rows;
+      if (*y1 > end - edge_rows) *y1 = end - edge_rows;
+    }
+  } else {
+    // uniform strips, boundary ones first: order 0 -> strip 0, order 1 -> last strip
+    const int strip = order == 0 ? 0 : (order == 1 ? nstrips - 1 : order - 1);
+    *y0 = first + (int64_t)strip * strip_rows;
+    *y1 = *y0 + strip_rows;
+    if (*y1 > end) *y1 = end;
+  }
+}
 
 }  // namespace gol

@@ -280,13 +280,11 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
 
 // One warp task of a fused pass: strip `strip` of column group `cg`.
 template <int K, int V>
-__device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int strip_rows,
-                                           int strip, int cg, int lane) {
-  const int ext_out = c.ext_in - K;
+__device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int64_t y0, int64_t y1,
+                                           int cg, int lane) {
   TaskGeom g;
-  g.y0 = -(int64_t)ext_out + (int64_t)strip * strip_rows;
-  g.y1 = g.y0 + strip_rows;
-  if (g.y1 > c.H + ext_out) g.y1 = c.H + ext_out;
+  g.y0 = y0;
+  g.y1 = y1;
 
   // my word column (torus wrap in x, also when the row has < 32 words)
   int64_t wi = (int64_t)cg * kValidLanes - 1 + lane;
@@ -335,13 +333,6 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int 
   }
 }
 
-// boundary strips first: order 0 -> strip 0, order 1 -> last strip, then the interior
-__device__ __forceinline__ int strip_of_order(int order, int nstrips) {
-  if (order == 0) return 0;
-  if (order == 1) return nstrips - 1;
-  return order - 1;
-}
-
 // Last CTA of a launch advances the slab's counters.
 __device__ __forceinline__ void finish_pass(SlabState* st, const PassParams& p, unsigned nctas) {
   __syncthreads();
@@ -372,7 +363,10 @@ __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* state
                                p.mul2, p.mul31);
     const int order = task / p.col_groups;
     const int cg = task - order * p.col_groups;
-    fused_task<K, V>(st, c, p.strip_rows, strip_of_order(order, p.nstrips), cg, lane);
+    const int ext_out = p.ext_in - K;
+    int64_t y0, y1;
+    strip_range(order, p.nstrips, -(int64_t)ext_out, c.H + ext_out, p.strip_rows, p.edge_rows, &y0, &y1);
+    fused_task<K, V>(st, c, y0, y1, cg, lane);
   }
   finish_pass(st, p, gridDim.x);
 }
@@ -538,12 +532,15 @@ __global__ void __launch_bounds__(MAXT, MINB) life_persistent_kernel(SlabState* 
           seen0 + (unsigned long long)nex * (unsigned long long)pp.depth * (unsigned long long)st->ws;
       const PassCtx c = make_ctx(st, pass0 + pass, exch, seen, ext_in, consume, push);
       const int64_t rows_total = c.H + 2 * ext_out;
-      const int nstrips = (int)((rows_total + pp.pass.strip_rows - 1) / pp.pass.strip_rows);
+      const int nstrips = strip_count(rows_total, pp.pass.strip_rows, pp.pass.edge_rows);
       const int ntasks = nstrips * pp.pass.col_groups;
       for (int task = gwarp; task < ntasks; task += nwarps) {
         const int order = task / pp.pass.col_groups;
         const int cg = task - order * pp.pass.col_groups;
-        fused_task<K, 0>(st, c, pp.pass.strip_rows, strip_of_order(order, nstrips), cg, lane);
+        int64_t y0, y1;
+        strip_range(order, nstrips, -(int64_t)ext_out, c.H + ext_out, pp.pass.strip_rows, pp.pass.edge_rows,
+                    &y0, &y1);
+        fused_task<K, 0>(st, c, y0, y1, cg, lane);
       }
     }
     grid_barrier(pp.barrier, gridDim.x, epoch);

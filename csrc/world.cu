@@ -193,7 +193,7 @@ int make_plan(gol_world* w) {
                      GOL_MAX_GHOST, depth, K);
   if (depth > w->H)
     return set_error(GOL_ERR_ARG, "exchange_depth %d exceeds the slab height %lld", depth, (long long)w->H);
-  int t = c.threads_per_block > 0 ? c.threads_per_block : 128;
+  int t = c.threads_per_block > 0 ? c.threads_per_block : 256;
   if (t < 1 || t > 1024)
     return set_error(GOL_ERR_ARG, "threads per block must be in [1,1024], got %d", t);
   t = std::max(32, (t / 32) * 32);  // whole warps
@@ -224,9 +224,11 @@ int finish_plan_cuda(gol_world* w) {
     const int ctas = persistent_max_ctas(p.temporal_k, p.threads_per_block, dev);
     if (ctas > 0) slots = ctas * wpb / std::max(1, slabs_per_dev);
   }
-  p.strip_rows = pick_strip_rows(w->H, p.col_groups, p.temporal_k, slots);
+  // the two edge strips (exchange_depth rows each) are tasks of their own; the interior is tuned
+  const int64_t interior = std::max<int64_t>(1, w->H - 2 * p.exchange_depth);
+  p.strip_rows = pick_strip_rows(interior, p.col_groups, p.temporal_k, std::max(1, slots - 2 * p.col_groups));
   const int wpb = p.threads_per_block / 32;
-  const int64_t strips = (w->H + p.strip_rows - 1) / p.strip_rows;
+  const int64_t strips = strip_count(w->H, p.strip_rows, p.exchange_depth);
   p.ctas_per_slab = (int)((strips * p.col_groups + wpb - 1) / wpb);
   p.regs_hint = rw;
   return GOL_OK;
@@ -237,7 +239,8 @@ void fill_strips(const gol_world* w, PassParams* pp) {
   const int64_t rows_total = w->H + 2 * ext_out;
   pp->strip_rows = w->plan.strip_rows;
   pp->col_groups = w->plan.col_groups;
-  pp->nstrips = (int)((rows_total + pp->strip_rows - 1) / pp->strip_rows);
+  pp->edge_rows = w->plan.exchange_depth;
+  pp->nstrips = strip_count(rows_total, pp->strip_rows, pp->edge_rows);
 }
 
 // The pass schedule for `gens` generations; identical on every rank.
@@ -850,6 +853,7 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
           pp.pass.ext_in = pl.exchange_depth;
           pp.pass.k = pl.temporal_k;
           pp.pass.strip_rows = pl.strip_rows;
+          pp.pass.edge_rows = pl.exchange_depth;
           pp.pass.col_groups = pl.col_groups;
           pp.npasses = (int)(now * P);
           pp.passes_per_exchange = P;
@@ -858,7 +862,7 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
           pp.barrier = g.d_barrier;
           const int wpb = pl.threads_per_block / 32;
           const int64_t rows_total = w->H + 2 * (pl.exchange_depth - pl.temporal_k);
-          const int64_t tasks = ((rows_total + pl.strip_rows - 1) / pl.strip_rows) * pl.col_groups;
+          const int64_t tasks = (int64_t)strip_count(rows_total, pl.strip_rows, pl.exchange_depth) * pl.col_groups;
           int nctas = persistent_max_ctas(pl.temporal_k, pl.threads_per_block, g.device);
           if (nctas < 1) return set_error(GOL_ERR_CUDA, "persistent kernel cannot be made resident");
           nctas = (int)std::min<int64_t>(nctas, (tasks + wpb - 1) / wpb);
