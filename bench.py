@@ -172,7 +172,8 @@ def run_ours(args) -> int:
     from gol_b200.utils.timing import flush_l2
 
     gens = args.gens
-    life = Life(args.size, args.size, mode=args.mode, k=args.k, depth=args.depth, threads=args.threads,
+    rows = args.rows or args.size
+    life = Life(args.size, rows, mode=args.mode, k=args.k, depth=args.depth, threads=args.threads,
                 distributed=distributed)
     stream = torch.cuda.Stream()          # a capturable (non-legacy) stream shared by torch and the core
     torch.cuda.set_stream(stream)
@@ -187,7 +188,7 @@ def run_ours(args) -> int:
 
     # pinned host copy of the initial world for the end-to-end arm
     stride = life.world.stride
-    host_words = torch.empty((args.size, stride), dtype=torch.int64).pin_memory()
+    host_words = torch.empty((rows, stride), dtype=torch.int64).pin_memory()
     nat.check(nat.lib.gol_world_read_packed(life.world._h, 0, host_words.data_ptr()))
     host_pop = torch.zeros(1, dtype=torch.int64).pin_memory()
 
@@ -232,7 +233,7 @@ def run_ours(args) -> int:
     if distributed:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms, e2e_ms = float(t[0]), float(t[1])
-    updates = float(world) * args.size * args.size * gens * args.steps
+    updates = float(world) * args.size * rows * gens * args.steps
     value = updates / (total_ms * 1e-3) * 1e-9
     e2e_value = updates / (e2e_ms * 1e-3) * 1e-9
 
@@ -246,8 +247,8 @@ def run_ours(args) -> int:
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "1-bit cells (uint64 x64 packed)",
             "data": "synthetic (random 50% density, counter-based hash, seed 1234)",
-            "config": {"model": "conway-life-torus", "cells_per_gpu": f"{args.size}x{args.size}",
-                       "generations_per_step": gens, "global_batch": world * args.size * args.size,
+            "config": {"model": "conway-life-torus", "cells_per_gpu": f"{args.size}x{rows}",
+                       "generations_per_step": gens, "global_batch": world * args.size * rows,
                        "parallelism": f"row-slab ring x{world}, one process per GPU, NVLink P2P halo fused in kernel",
                        "mode": plan["mode_name"], "k": plan["temporal_k"], "exchange_depth": plan["exchange_depth"],
                        "threads_per_block": plan["threads_per_block"], "strip_rows": plan["strip_rows"],
@@ -272,13 +273,61 @@ def run_ours(args) -> int:
     return 0
 
 
+# ---------------------------------------------------------------------------- NCCL baseline arm
+def run_nccl_baseline(args) -> int:
+    """Library-collective baseline: ncclSend/ncclRecv halo + unfused stencil kernel per generation
+    (gol_b200.parallel.nccl_halo).  Not the product path; measured for comparison only."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local_rank = env_rank()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    else:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1,
+                                device_id=torch.device("cuda", local_rank))
+    from gol_b200.models.patterns import pattern_bytes
+    from gol_b200.parallel.nccl_halo import NcclHaloStepper
+
+    rows = args.rows or args.size
+    gens = min(args.gens, 64)
+    st = NcclHaloStepper(args.size, rows)
+    small = torch.from_numpy(pattern_bytes(6, args.size, 64, rank, world, seed=1234)).cuda()
+    st.load(small.repeat(rows // 64, 1))
+    for _ in range(args.warmup):
+        st.step(8)
+    dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        st.step(gens)
+    b.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0])
+    if rank == 0:
+        updates = float(world) * args.size * rows * gens * args.steps
+        print(json.dumps({"impl": "nccl-baseline", "metric": METRIC, "value": updates / (ms * 1e-3) * 1e-9,
+                          "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "ms_per_step": ms / args.steps,
+                          "config": {"cells_per_gpu": f"{args.size}x{rows}", "generations_per_step": gens,
+                                     "halo": "dist.batch_isend_irecv (ncclSend/ncclRecv) every generation",
+                                     "stencil": "step_rows_kernel (unfused, bit-packed, 1 generation)"}}), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"])
     ap.add_argument("--size", type=int, default=SIZE)
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: square, = --size)")
     ap.add_argument("--gens", type=int, default=GENS_PER_STEP)
     ap.add_argument("--mode", default="auto")
     ap.add_argument("--k", type=int, default=0)
@@ -294,6 +343,8 @@ def main() -> int:
         args.warmup = 3
     if args.impl == "reference":
         return run_reference(args)
+    if args.impl == "nccl":
+        return run_nccl_baseline(args)
     return run_ours(args)
 
 

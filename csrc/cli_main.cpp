@@ -25,7 +25,7 @@ static void die(const char* what) {
 
 int main(int argc, char** argv) {
   std::vector<const char*> pos;
-  int ranks = 1, mode = GOL_MODE_AUTO, k = 0, depth = 0, cpu = 0, check = 0, json = 0, ndev = 0;
+  int ranks = 1, mode = GOL_MODE_AUTO, k = 0, depth = 0, cpu = 0, check = 0, json = 0, ndev = 0, strip = 0;
   long long rows = 0;
   double density = 0.5;
   unsigned long long seed = 1;
@@ -44,6 +44,7 @@ int main(int argc, char** argv) {
     else if (a == "--k") k = atoi(val("--k"));
     else if (a == "--depth") depth = atoi(val("--depth"));
     else if (a == "--devices") ndev = atoi(val("--devices"));
+    else if (a == "--strip") strip = atoi(val("--strip"));
     else if (a == "--density") density = atof(val("--density"));
     else if (a == "--seed") seed = strtoull(val("--seed"), nullptr, 10);
     else if (a == "--outdir") outdir = val("--outdir");
@@ -99,6 +100,7 @@ int main(int argc, char** argv) {
   cfg.exchange_depth = depth;
   cfg.threads_per_block = threads;
   cfg.ndevices = ndev;
+  cfg.reserved = strip;
 
   gol_world_t* w = gol_world_create(&cfg);
   if (!w) die("cannot create world");

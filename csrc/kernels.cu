@@ -16,6 +16,7 @@
 // red.release.sys; the warps that need a fresh halo spin on ld.acquire.sys.
 // Those warps are scheduled first (lowest task ids).
 #include <stdlib.h>
+#include <string.h>
 
 #include "kernels.cuh"
 
@@ -279,20 +280,51 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
 }
 
 // One warp task of a fused pass: strip `strip` of column group `cg`.
-template <int K, int V>
-__device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int64_t y0, int64_t y1,
-                                           int cg, int lane) {
+__device__ __forceinline__ TaskGeom make_geom(const PassCtx& c, int64_t y0, int64_t y1, int cg, int lane) {
   TaskGeom g;
   g.y0 = y0;
   g.y1 = y1;
-
   // my word column (torus wrap in x, also when the row has < 32 words)
   int64_t wi = (int64_t)cg * kValidLanes - 1 + lane;
   wi %= c.ws;
   if (wi < 0) wi += c.ws;
   g.wi = wi;
   g.owner = lane >= 1 && lane <= kValidLanes && ((int64_t)cg * kValidLanes + lane - 1) < c.ws;
+  return g;
+}
 
+// Halo push (fused MPI_Isend, gol-main.c:104-107): the rows this task just produced that the
+// ring neighbours need go straight into their recv buffers, then the word count is published.
+__device__ __forceinline__ void push_edges(SlabState* st, const PassCtx& c, const TaskGeom& g, int lane) {
+  if (!c.push) return;
+  const int64_t t0 = g.y0 > 0 ? g.y0 : 0;
+  const int64_t t1 = g.y1 < c.push ? g.y1 : c.push;              // rows [0, push) -> prev
+  const int64_t b0 = g.y0 > c.H - c.push ? g.y0 : c.H - c.push;  // rows [H-push, H) -> next
+  const int64_t b1 = g.y1 < c.H ? g.y1 : c.H;
+  const int rows_top = t1 > t0 ? (int)(t1 - t0) : 0;
+  const int rows_bot = b1 > b0 ? (int)(b1 - b0) : 0;
+  if (rows_top | rows_bot) {
+    if (g.owner) {
+      const uint64_t* mine = c.out + g.wi;
+      for (int64_t y = t0; y < t1; ++y) st_cg(c.ptop + y * c.stride + g.wi, ld_cg(mine + y * c.stride));
+      for (int64_t y = b0; y < b1; ++y)
+        st_cg(c.pbot + (y - (c.H - c.push)) * c.stride + g.wi, ld_cg(mine + y * c.stride));
+    }
+    __threadfence_system();
+    __syncwarp();
+    const unsigned owners = __popc(__ballot_sync(kFull, g.owner));
+    if (lane == 0) {
+      if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
+      if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
+    }
+  }
+}
+
+// One warp task of a fused pass: output rows [y0, y1) of column group `cg`.
+template <int K, int V>
+__device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int64_t y0, int64_t y1,
+                                           int cg, int lane) {
+  const TaskGeom g = make_geom(c, y0, y1, cg, lane);
   const bool reads_top = c.consume && (g.y0 - K < 0);
   const bool reads_bot = c.consume && (g.y1 + K > c.H);
   if (reads_top || reads_bot) {
@@ -305,32 +337,7 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int6
   } else {
     stream_rows<K, V, false>(c, g);
   }
-
-  // Halo push (fused MPI_Isend, gol-main.c:104-107): the rows this task just produced that the
-  // ring neighbours need go straight into their recv buffers, then the word count is published.
-  if (c.push) {
-    const int64_t t0 = g.y0 > 0 ? g.y0 : 0;
-    const int64_t t1 = g.y1 < c.push ? g.y1 : c.push;              // rows [0, push) -> prev
-    const int64_t b0 = g.y0 > c.H - c.push ? g.y0 : c.H - c.push;  // rows [H-push, H) -> next
-    const int64_t b1 = g.y1 < c.H ? g.y1 : c.H;
-    const int rows_top = t1 > t0 ? (int)(t1 - t0) : 0;
-    const int rows_bot = b1 > b0 ? (int)(b1 - b0) : 0;
-    if (rows_top | rows_bot) {
-      if (g.owner) {
-        const uint64_t* mine = c.out + wi;
-        for (int64_t y = t0; y < t1; ++y) st_cg(c.ptop + y * c.stride + wi, ld_cg(mine + y * c.stride));
-        for (int64_t y = b0; y < b1; ++y)
-          st_cg(c.pbot + (y - (c.H - c.push)) * c.stride + wi, ld_cg(mine + y * c.stride));
-      }
-      __threadfence_system();
-      __syncwarp();
-      const unsigned owners = __popc(__ballot_sync(kFull, g.owner));
-      if (lane == 0) {
-        if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
-        if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
-      }
-    }
-  }
+  push_edges(st, c, g, lane);
 }
 
 // Last CTA of a launch advances the slab's counters.
@@ -351,8 +358,17 @@ __device__ __forceinline__ void finish_pass(SlabState* st, const PassParams& p, 
   }
 }
 
+// Programmatic dependent launch: when the host launches with the PDL attribute, this grid may be
+// scheduled while its predecessor drains; nothing of the predecessor's output (not even the pass
+// counters) is read before griddepcontrol.wait.  Without the attribute both are no-ops.
+__device__ __forceinline__ void pdl_wait_and_release() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 template <int K, int MAXT, int MINB, int V>
 __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* states, PassParams p) {
+  pdl_wait_and_release();
   SlabState* st = states + blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
@@ -367,6 +383,189 @@ __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* state
     int64_t y0, y1;
     strip_range(order, p.nstrips, -(int64_t)ext_out, c.H + ext_out, p.strip_rows, p.edge_rows, &y0, &y1);
     fused_task<K, V>(st, c, y0, y1, cg, lane);
+  }
+  finish_pass(st, p, gridDim.x);
+}
+
+// ---- N-K1 (TMA-fed): input rows arrive through the tensor memory accelerator ---------------------
+// Same K-stage register pipeline, but the interior strips issue no LDGs: one elected thread per
+// CTA streams 8-row x 144-word boxes global -> shared with cp.async.bulk.tensor.2d (SASS:
+// UTMALDG) through a tensor map of the slab, into a 3-slot ring guarded by full/empty
+// mbarriers; the four compute warps read their word with one conflict-free LDS.64 per row.
+// The CTA tile is one strip x 4 adjacent column groups: words [120*c4 - 1, 120*c4 + 121), box
+// start rounded down to 128 bytes.  TMA cannot wrap around the torus seam: columns outside
+// [0, ws) arrive zero-filled, and the only two out-of-range words that matter (the halo word
+// left of column 0 and right of column W-1) are fetched by their lane with a plain load.
+// (A first version used one 1 KB cp.async.bulk per row: correct, but the per-SM copy engine
+// retires roughly one descriptor per 200 cycles, which starved the pipeline: 9.5 vs 26.6 TCUPS.)
+// Edge strips (the ones that read freshly exchanged halo rows) keep the LDG path: their data
+// was just written by a peer GPU and is consumed through ld.acquire ordering.
+namespace tma {
+// NW compute warps per CTA (3 or 4, whichever wastes fewer column groups); box width in words:
+// NW*30 + 2 needed, plus up to 15 because the box start is rounded down to 128 bytes
+__host__ __device__ constexpr int seg_words(int nw) { return (nw * kValidLanes + 2 + 15 + 15) / 16 * 16; }  // 4 -> 144, 3 -> 112
+constexpr int kChunk = 8;    // box height = rows per ring slot
+constexpr int kSlots = 5;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Wait for a phase by polling test_wait.  Measured on B200 for this kernel (16384^2 / 65536-wide):
+// suspending mbarrier.try_wait, with or without a suspend-time hint: 7-9 / 11 TCUPS; one polling
+// lane + __syncwarp: 8 / 10; every thread polling test_wait: 15 / 29 with 3 ring slots and
+// 17 / 30 with 5.  The LDG path does 26.8 / 33.0.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_test(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void tensor_g2s(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tensor3_g2s(void* dst, const CUtensorMap* map, int x, int j, int y, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(x), "r"(j), "r"(y), "r"(smem_u32(bar))
+      : "memory");
+}
+}  // namespace tma
+
+template <int K, int NW>
+__global__ void __launch_bounds__(NW * 32, 512 / (NW * 32))
+    life_fused_tma_kernel(SlabState* states, PassParams p, const CUtensorMap* tmaps) {
+  using namespace tma;
+  constexpr int kWarps = NW;
+  constexpr int kSeg = seg_words(NW);
+  static_assert(2 * K <= kChunk, "pipeline fill must fit the first chunk");
+  __shared__ __align__(128) uint64_t ring[kSlots][kChunk][kSeg];
+  __shared__ __align__(8) uint64_t full_bar[kSlots];
+  __shared__ __align__(8) uint64_t empty_bar[kSlots];
+
+  pdl_wait_and_release();
+  SlabState* st = states + blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ncg4 = (p.col_groups + kWarps - 1) / kWarps;
+  const int order = blockIdx.x / ncg4;
+  const int c4 = blockIdx.x - order * ncg4;
+  const unsigned long long pass = st->pass;
+  const PassCtx c = make_ctx(st, pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push);
+  const int ext_out = p.ext_in - K;
+  int64_t y0, y1;
+  strip_range(order, p.nstrips, -(int64_t)ext_out, c.H + ext_out, p.strip_rows, p.edge_rows, &y0, &y1);
+  const int cg = c4 * kWarps + warp;
+  const bool edge = c.consume && (y0 - K < 0 || y1 + K > c.H);
+
+  if (edge) {
+    if (cg < p.col_groups) fused_task<K, 0>(st, c, y0, y1, cg, lane);
+  } else {
+    const int n_in = (int)(y1 - y0) + 2 * K;
+    const int nchunks = (n_in + kChunk - 1) / kChunk;
+    const int64_t y_in = y0 - K;
+    const CUtensorMap* map = tmaps + 2 * blockIdx.y + (pass & 1);  // the input buffer's map
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < kSlots; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], kWarps);
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int64_t need = (int64_t)c4 * (kWarps * kValidLanes) - 1;   // first word this CTA reads (halo)
+    const int64_t seg_start = need & ~int64_t(15);                    // box x: 128-byte aligned, may be -16
+    const int row0 = st->G + (int)y_in;                               // box y of chunk 0 in buffer rows
+    auto issue_chunk = [&](int ch) {
+      const int slot = ch % kSlots;
+      mbar_expect_tx(&full_bar[slot], (uint32_t)(kChunk * kSeg * 8));
+      if (p.tma_rank == 3)   // rows viewed as [ws/16][16 words]: 128-byte inner box
+        tensor3_g2s(&ring[slot][0][0], map, 0, (int)(seg_start >> 4), row0 + ch * kChunk, &full_bar[slot]);
+      else
+        tensor_g2s(&ring[slot][0][0], map, (int)seg_start, row0 + ch * kChunk, &full_bar[slot]);
+    };
+    if (threadIdx.x == 0)
+      for (int ch = 0; ch < kSlots && ch < nchunks; ++ch) issue_chunk(ch);
+
+    const TaskGeom g = make_geom(c, y0, y1, cg, lane);
+    uint64_t* out_col = c.out + g.wi;
+    const int off = warp * kValidLanes + lane + (int)(need - seg_start);  // my word inside the box
+    // the two words TMA cannot deliver: column -1 (= ws-1) and column ws (= 0)
+    const int64_t gw = need + warp * kValidLanes + lane;
+    const bool seam = (gw == -1) || (gw == c.ws);
+    const uint64_t* seam_col = c.in + (gw < 0 ? c.ws - 1 : 0);
+    Stage s[K];
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+      s[t].lo.a0 = s[t].lo.a1 = s[t].lo.b0 = s[t].lo.b1 = s[t].lo.c = 0;
+      s[t].hi.a0 = s[t].hi.a1 = s[t].hi.b0 = s[t].hi.b1 = s[t].hi.c = 0;
+    }
+
+    for (int ch = 0; ch < nchunks; ++ch) {
+      const int slot = ch % kSlots;
+      uint64_t rows[kChunk];
+      if (seam) {  // issued before the barrier wait so that the latency overlaps it
+#pragma unroll
+        for (int r = 0; r < kChunk; ++r) {
+          int i = ch * kChunk + r;
+          i = i < n_in - 1 ? i : n_in - 1;
+          rows[r] = ld_cg(seam_col + (y_in + i) * c.stride);
+        }
+      }
+      mbar_wait(&full_bar[slot], (uint32_t)((ch / kSlots) & 1));
+      if (!seam) {
+#pragma unroll
+        for (int r = 0; r < kChunk; ++r) rows[r] = ring[slot][r][off];
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[slot]);   // my warp no longer needs this slot
+      if (threadIdx.x == 0 && ch + kSlots < nchunks) {
+        mbar_wait(&empty_bar[slot], (uint32_t)((ch / kSlots) & 1));  // all four warps released it
+        issue_chunk(ch + kSlots);
+      }
+      __syncwarp();  // reconverge after the single-lane sections: the stages below shuffle
+      if (ch == 0) {
+#pragma unroll
+        for (int r = 0; r < kChunk; ++r) {
+          if (r < 2 * K) {
+            push_row<K, 0>(s, rows[r], (r / 2 + 1 < K) ? r / 2 + 1 : K, 2u, 0x80000000u);
+          } else {
+            const uint64_t o = push_row<K, 0>(s, rows[r], K, 2u, 0x80000000u);
+            const int64_t y = y0 + (r - 2 * K);
+            if (g.owner && y < y1) st_cg(out_col + y * c.stride, o);
+          }
+        }
+      } else {
+        const int64_t yb = y0 + (int64_t)ch * kChunk - 2 * K;
+#pragma unroll
+        for (int r = 0; r < kChunk; ++r) {
+          const uint64_t o = push_row<K, 0>(s, rows[r], K, 2u, 0x80000000u);
+          const int64_t y = yb + r;
+          if (g.owner && y < y1) st_cg(out_col + y * c.stride, o);
+        }
+      }
+    }
+    if (cg < p.col_groups) push_edges(st, c, g, lane);
   }
   finish_pass(st, p, gridDim.x);
 }
@@ -795,6 +994,16 @@ static int fused_variant() {
   return v;
 }
 
+// GOL_PDL=1: launch fused passes with programmatic dependent launch.
+static bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GOL_PDL");
+    v = e ? atoi(e) : 0;
+  }
+  return v != 0;
+}
+
 bool fused_k_supported(int K) { return K == 1 || K == 2 || K == 3 || K == 4 || K == 6 || K == 8; }
 
 FusedLimits fused_limits(int K) {
@@ -843,7 +1052,64 @@ cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParam
   pp.mul31 = 0x80000000u;
   void* args[] = {(void*)&d_states, (void*)&pp};
   count_launch(1);
+  if (pdl_enabled()) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelExC(&cfg, fn, args);
+  }
   return cudaLaunchKernel(fn, grid, dim3((unsigned)threads), args, 0, s);
+}
+
+bool fused_tma_supported(int K, int64_t ws) {
+  return K >= 1 && K <= 4 && (ws % 16) == 0 && ws >= tma::seg_words(4);
+}
+// 3 or 4 compute warps per CTA: the count that leaves fewer idle column groups (9 groups -> 3 x 3)
+int fused_tma_warps(int col_groups) {
+  const int w4 = (col_groups + 3) / 4 * 4, w3 = (col_groups + 2) / 3 * 3;
+  return w3 < w4 ? 3 : 4;
+}
+int fused_tma_box_words(int nw) { return nw == 3 ? tma::seg_words(3) : tma::seg_words(4); }
+int fused_tma_box_rows() { return tma::kChunk; }
+
+int fused_tma_rank() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GOL_TMA_RANK");
+    v = (e && atoi(e) == 2) ? 2 : 3;
+  }
+  return v;
+}
+
+cudaError_t launch_fused_tma(int K, SlabState* d_states, int nslabs, const PassParams& p0,
+                             const CUtensorMap* d_tmaps, cudaStream_t s) {
+  PassParams p = p0;
+  p.tma_rank = fused_tma_rank();
+  const int nw = fused_tma_warps(p.col_groups);
+  const int ncg4 = (p.col_groups + nw - 1) / nw;
+  dim3 grid((unsigned)(p.nstrips * ncg4), (unsigned)nslabs);
+  dim3 block((unsigned)nw * 32);
+  count_launch(1);
+#define GOL_TMA_CASE(KK)                                                                      \
+  case KK:                                                                                    \
+    if (nw == 3) life_fused_tma_kernel<KK, 3><<<grid, block, 0, s>>>(d_states, p, d_tmaps);   \
+    else life_fused_tma_kernel<KK, 4><<<grid, block, 0, s>>>(d_states, p, d_tmaps);           \
+    break;
+  switch (K) {
+    GOL_TMA_CASE(1)
+    GOL_TMA_CASE(2)
+    GOL_TMA_CASE(3)
+    GOL_TMA_CASE(4)
+    default: return cudaErrorInvalidValue;
+  }
+#undef GOL_TMA_CASE
+  return cudaGetLastError();
 }
 
 cudaError_t launch_generic(SlabState* d_states, int nslabs, const PassParams& p, int threads,

@@ -1,5 +1,6 @@
 // kernels.cuh — host-callable launch wrappers of every device kernel.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -29,6 +30,16 @@ int persistent_max_ctas(int K, int threads, int device);
 
 cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParams& p, int threads,
                          cudaStream_t s);
+// TMA-fed variant (K <= 4, ws % 16 == 0, ws >= 144): interior strips fed by 2-D tensor copies
+// (cp.async.bulk.tensor) into an mbarrier ring.  d_tmaps: device array [nslabs][2] of tensor
+// maps over buf[0] / buf[1] of each slab (box fused_tma_box_words(nw) x fused_tma_box_rows()).
+bool fused_tma_supported(int K, int64_t ws);
+int fused_tma_warps(int col_groups);   // compute warps per CTA (3 or 4)
+int fused_tma_box_words(int nw);
+int fused_tma_box_rows();
+int fused_tma_rank();  // 2 or 3 (GOL_TMA_RANK), see make_tensor_maps
+cudaError_t launch_fused_tma(int K, SlabState* d_states, int nslabs, const PassParams& p,
+                             const CUtensorMap* d_tmaps, cudaStream_t s);
 cudaError_t launch_generic(SlabState* d_states, int nslabs, const PassParams& p, int threads,
                            int64_t max_words, cudaStream_t s);
 cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max_ws, cudaStream_t s);

@@ -77,6 +77,7 @@ struct Group {
   std::vector<int> slabs;
   SlabState* d_states = nullptr;
   unsigned int* d_barrier = nullptr;
+  CUtensorMap* d_tmaps = nullptr;  // [slabs][2], TMA mode only
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   std::map<int64_t, std::pair<cudaGraphExec_t, int>> graphs;  // gens -> (exec, kernels)
 };
@@ -169,7 +170,6 @@ int make_plan(gol_world* w) {
       mode = GOL_MODE_GENERIC;
     }
   }
-  if (mode == GOL_MODE_TMA) mode = GOL_MODE_FUSED;  // TMA-fed variant selects itself inside the fused path
   if (mode == GOL_MODE_GENERIC) {
     int t = c.threads_per_block > 0 ? c.threads_per_block : 256;
     if (t < 1 || t > 1024)
@@ -199,6 +199,13 @@ int make_plan(gol_world* w) {
   t = std::max(32, (t / 32) * 32);  // whole warps
   const int lim = fused_limits(K).max_threads;
   if (t > lim) t = lim;             // register budget of the K-generation pipeline
+  if (mode == GOL_MODE_TMA) {
+    if (!fused_tma_supported(K, w->ws))
+      return set_error(GOL_ERR_UNSUPPORTED,
+                       "mode tma needs temporal_k <= 4 and a width that is a multiple of 1024 and >= 9216 "
+                       "(128-byte aligned 144-word row segments); got k=%d width=%lld", K, (long long)w->W);
+    t = 32 * fused_tma_warps((int)((w->ws + 29) / 30));   // CTA tile = 3 or 4 column groups
+  }
   p.mode = mode;
   p.temporal_k = K;
   p.exchange_depth = depth;
@@ -210,7 +217,7 @@ int make_plan(gol_world* w) {
 
 int finish_plan_cuda(gol_world* w) {
   gol_plan_t& p = w->plan;
-  if (p.mode != GOL_MODE_FUSED && p.mode != GOL_MODE_PERSISTENT) return GOL_OK;
+  if (p.mode != GOL_MODE_FUSED && p.mode != GOL_MODE_PERSISTENT && p.mode != GOL_MODE_TMA) return GOL_OK;
   const int dev = w->groups.empty() ? 0 : w->groups[0].device;
   CU_TRY(cudaSetDevice(dev));
   CU_TRY(cudaDeviceGetAttribute(&w->sms, cudaDevAttrMultiProcessorCount, dev));
@@ -226,11 +233,66 @@ int finish_plan_cuda(gol_world* w) {
   }
   // the two edge strips (exchange_depth rows each) are tasks of their own; the interior is tuned
   const int64_t interior = std::max<int64_t>(1, w->H - 2 * p.exchange_depth);
-  p.strip_rows = pick_strip_rows(interior, p.col_groups, p.temporal_k, std::max(1, slots - 2 * p.col_groups));
+  // in TMA mode a CTA always carries a fixed number (3 or 4) of column groups
+  const int tw = fused_tma_warps(p.col_groups);
+  const int cg_eff = p.mode == GOL_MODE_TMA ? (p.col_groups + tw - 1) / tw * tw : p.col_groups;
+  p.strip_rows = pick_strip_rows(interior, cg_eff, p.temporal_k, std::max(1, slots - 2 * cg_eff));
+  if (w->cfg.reserved > 0) p.strip_rows = w->cfg.reserved;   // explicit strip height (tuning / experiments)
   const int wpb = p.threads_per_block / 32;
   const int64_t strips = strip_count(w->H, p.strip_rows, p.exchange_depth);
   p.ctas_per_slab = (int)((strips * p.col_groups + wpb - 1) / wpb);
   p.regs_hint = rw;
+  return GOL_OK;
+}
+
+// Tensor maps (TMA descriptors) over both buffers of every slab: uint64 elements, dims
+// {ws, H + 2G}, row pitch = stride words, box = 144 words x 8 rows, no swizzle, zero fill
+// outside the tensor.  cuTensorMapEncodeTiled is a driver entry point; it is looked up through
+// the runtime so that the library does not link libcuda.
+int make_tensor_maps(gol_world* w) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                               const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                               CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  CU_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+  if (!fn || q != cudaDriverEntryPointSuccess)
+    return set_error(GOL_ERR_UNSUPPORTED, "driver has no cuTensorMapEncodeTiled");
+  EncodeFn encode = (EncodeFn)fn;
+  const int box_words = fused_tma_box_words(fused_tma_warps(w->plan.col_groups));
+  if (w->H + 2 * w->G < fused_tma_box_rows())
+    return set_error(GOL_ERR_UNSUPPORTED, "mode tma needs at least %d buffer rows", fused_tma_box_rows());
+  for (auto& g : w->groups) {
+    CU_TRY(cudaSetDevice(g.device));
+    std::vector<CUtensorMap> maps(g.slabs.size() * 2);
+    for (size_t i = 0; i < g.slabs.size(); ++i) {
+      const Slab& sl = w->slabs[(size_t)g.slabs[i]];
+      for (int b = 0; b < 2; ++b) {
+        CUresult r;
+        if (fused_tma_rank() == 3) {
+          // each row as ws/16 groups of 16 words: the inner box extent is one 128-byte line
+          const cuuint64_t dims[3] = {16, (cuuint64_t)(w->ws / 16), (cuuint64_t)(w->H + 2 * w->G)};
+          const cuuint64_t strides[2] = {128, (cuuint64_t)w->stride * 8};
+          const cuuint32_t box[3] = {16, (cuuint32_t)(box_words / 16), (cuuint32_t)fused_tma_box_rows()};
+          const cuuint32_t estr[3] = {1, 1, 1};
+          r = encode(&maps[i * 2 + (size_t)b], CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, (void*)sl.h.buf[b], dims, strides,
+                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        } else {
+          const cuuint64_t dims[2] = {(cuuint64_t)w->ws, (cuuint64_t)(w->H + 2 * w->G)};
+          const cuuint64_t strides[1] = {(cuuint64_t)w->stride * 8};
+          const cuuint32_t box[2] = {(cuuint32_t)box_words, (cuuint32_t)fused_tma_box_rows()};
+          const cuuint32_t estr[2] = {1, 1};
+          r = encode(&maps[i * 2 + (size_t)b], CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, (void*)sl.h.buf[b], dims, strides,
+                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        }
+        if (r != CUDA_SUCCESS) return set_error(GOL_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", (int)r);
+      }
+    }
+    CU_TRY(cudaMalloc((void**)&g.d_tmaps, maps.size() * sizeof(CUtensorMap)));
+    CU_TRY(cudaMemcpy(g.d_tmaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+  }
   return GOL_OK;
 }
 
@@ -305,6 +367,8 @@ int launch_item(gol_world* w, Group& g, const PassItem& it) {
     e = launch_prime(g.d_states, n, it.depth, w->ws, g.stream);
   } else if (it.generic) {
     e = launch_generic(g.d_states, n, it.p, w->plan.threads_per_block, w->H * w->ws, g.stream);
+  } else if (w->plan.mode == GOL_MODE_TMA && fused_tma_supported(it.K, w->ws)) {
+    e = launch_fused_tma(it.K, g.d_states, n, it.p, g.d_tmaps, g.stream);
   } else {
     e = launch_fused(it.K, g.d_states, n, it.p, w->plan.threads_per_block, g.stream);
   }
@@ -500,6 +564,7 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
     }
   }
   if (finish_plan_cuda(w) != GOL_OK) return fail();
+  if (w->plan.mode == GOL_MODE_TMA && make_tensor_maps(w) != GOL_OK) return fail();
   return w;
 }
 
@@ -514,6 +579,7 @@ void gol_world_destroy(gol_world_t* w) {
       if (g.e1) cudaEventDestroy(g.e1);
       if (g.d_states) cudaFree(g.d_states);
       if (g.d_barrier) cudaFree(g.d_barrier);
+      if (g.d_tmaps) cudaFree(g.d_tmaps);
       if (g.own_stream && g.stream) cudaStreamDestroy(g.stream);
     }
     for (auto& p : w->peers)

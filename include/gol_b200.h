@@ -92,7 +92,7 @@ typedef struct gol_config {
   int32_t ndevices;       /* devices to spread local ranks over; 0 = all        */
   int32_t device_base;    /* local rank i -> device (device_base+i) % ndevices  */
   int32_t flags;          /* GOL_FLAG_*                                         */
-  int32_t reserved;
+  int32_t reserved;       /* > 0: force the strip height (rows per warp task) of the fused kernels */
 } gol_config_t;
 
 #define GOL_FLAG_NO_GRAPH 1      /* launch passes one by one, no CUDA graph     */

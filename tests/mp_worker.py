@@ -26,6 +26,7 @@ def main() -> int:
         ("fused", 4, 16, 1024, 128, 50, 6),
         ("fused", 8, 8, 4096, 512, 24, 6),
         ("fused", 1, 1, 256, 64, 19, 4),
+        ("tma", 4, 4, 10240, 256, 29, 6),
         ("persistent", 4, 4, 2048, 256, 43, 6),
         ("persistent", 2, 8, 1024, 128, 40, 5),
         ("generic", 0, 0, 200, 33, 9, 6),

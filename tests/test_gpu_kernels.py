@@ -135,6 +135,26 @@ def test_larger_world_against_packed_cpu_stepper():
     assert (got == expected(6, 8192, 1024, 2, 32, seed=77)).all()
 
 
+# ------------------------------------------------------------------ TMA-fed fused kernel
+@pytest.mark.parametrize("K", [1, 2, 3, 4])
+@pytest.mark.parametrize("W,H,R", [(10240, 100, 2), (9216, 64, 1), (16384, 300, 3), (11264, 41, 2)])
+def test_tma_fed_kernel(K, W, H, R):
+    # rows arrive through cp.async.bulk + mbarrier ring; 144-word CTA segments wrap the torus seam
+    gens = 3 * K + 5
+    got, plan = run_gpu(6, W, H, R, gens, mode="tma", k=K, seed=W + K)
+    assert plan["mode_name"] == "tma" and plan["threads_per_block"] in (96, 128)
+    assert (got == expected(6, W, H, R, gens, seed=W + K)).all()
+
+
+def test_tma_mode_deep_halo_and_rejections():
+    got, _ = run_gpu(6, 10240, 96, 2, 37, mode="tma", k=4, depth=16, seed=3)
+    assert (got == expected(6, 10240, 96, 2, 37, seed=3)).all()
+    with pytest.raises(GolError, match="mode tma"):
+        World(1024, 64, backend="cuda", mode="tma")          # too narrow for a 124-word segment
+    with pytest.raises(GolError, match="mode tma"):
+        World(16384, 64, backend="cuda", mode="tma", k=8)
+
+
 # ------------------------------------------------------------------ persistent kernel (N-K3)
 @pytest.mark.parametrize("k,depth,R", [(4, 4, 1), (4, 4, 2), (2, 8, 3), (8, 8, 2), (1, 1, 2)])
 def test_persistent_kernel(k, depth, R):
