@@ -282,11 +282,10 @@ def run_nccl_baseline(args) -> int:
 
     rank, world, local_rank = env_rank()
     torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    else:
-        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29533", rank=0, world_size=1,
-                                device_id=torch.device("cuda", local_rank))
+    if "RANK" not in os.environ:      # plain `python bench.py --impl nccl`: a one-rank group
+        os.environ.update(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0", MASTER_ADDR="127.0.0.1",
+                          MASTER_PORT=os.environ.get("MASTER_PORT", "29533"))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from gol_b200.models.patterns import pattern_bytes
     from gol_b200.parallel.nccl_halo import NcclHaloStepper
 

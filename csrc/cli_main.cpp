@@ -102,6 +102,21 @@ int main(int argc, char** argv) {
   cfg.ndevices = ndev;
   cfg.reserved = strip;
 
+  if (on_off == 1) {
+    // like the reference, open every rank's output file before any work (gol-main.c:64-73)
+    for (int r = 0; r < ranks; ++r) {
+      char name[64];
+      gol_rank_file_name(name, sizeof name, r, ranks);
+      const std::string path = outdir ? std::string(outdir) + "/" + name : std::string(name);
+      FILE* fp = fopen(path.c_str(), "w");
+      if (!fp) {
+        printf("ERROR IN RANK %d", r);
+        return 255;
+      }
+      fclose(fp);
+    }
+  }
+
   gol_world_t* w = gol_world_create(&cfg);
   if (!w) die("cannot create world");
   if (gol_world_connect(w)) die("connect");

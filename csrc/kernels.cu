@@ -310,7 +310,10 @@ __device__ __forceinline__ void push_edges(SlabState* st, const PassCtx& c, cons
       for (int64_t y = b0; y < b1; ++y)
         st_cg(c.pbot + (y - (c.H - c.push)) * c.stride + g.wi, ld_cg(mine + y * c.stride));
     }
-    __threadfence_system();
+    // No per-lane fence: the warp barrier orders every lane's stores before lane 0's
+    // red.release.sys, and a release is cumulative over what happens-before it.  (A per-lane
+    // __threadfence_system() is a fence.sc.sys; it kept the edge warp, and with it the kernel,
+    // alive for an extra NVLink round trip or more: ~9 us per pass on the 4096^2 config.)
     __syncwarp();
     const unsigned owners = __popc(__ballot_sync(kFull, g.owner));
     if (lane == 0) {
@@ -344,7 +347,6 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int6
 __device__ __forceinline__ void finish_pass(SlabState* st, const PassParams& p, unsigned nctas) {
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence();
     const unsigned prev = atomicAdd(&st->done, 1u);
     if (prev == nctas - 1) {
       st->done = 0;
@@ -606,8 +608,7 @@ __global__ void life_generic_kernel(SlabState* states, PassParams p) {
     }
   }
   if (p.push) {
-    if (sent_top | sent_bot) __threadfence_system();
-    const int nt = __syncthreads_count(sent_top);
+    const int nt = __syncthreads_count(sent_top);   // block barrier + cumulative release below
     const int nb = __syncthreads_count(sent_bot);
     if (threadIdx.x == 0) {
       if (nt) red_release_sys_add(st->peer_flag[0], (unsigned long long)nt);
@@ -641,7 +642,6 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
       ++sent_bot;
     }
   }
-  if (sent_top | sent_bot) __threadfence_system();
   __shared__ unsigned long long acc[2];
   if (threadIdx.x == 0) acc[0] = acc[1] = 0;
   __syncthreads();
@@ -708,11 +708,18 @@ __global__ void __launch_bounds__(MAXT, MINB) life_persistent_kernel(SlabState* 
           ++sent_bot;
         }
       }
-      if (sent_top | sent_bot) {
-        __threadfence_system();
-        if (sent_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)sent_top);
-        if (sent_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)sent_bot);
+      // publish once per CTA: block barrier, then one cumulative release by thread 0
+      __shared__ unsigned long long acc[2];
+      if (threadIdx.x == 0) acc[0] = acc[1] = 0;
+      __syncthreads();
+      if (sent_top) atomicAdd(&acc[0], (unsigned long long)sent_top);
+      if (sent_bot) atomicAdd(&acc[1], (unsigned long long)sent_bot);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        if (acc[0]) red_release_sys_add(st->peer_flag[0], acc[0]);
+        if (acc[1]) red_release_sys_add(st->peer_flag[1], acc[1]);
       }
+      __syncthreads();
     }
   }
 

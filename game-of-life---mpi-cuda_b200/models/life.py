@@ -161,6 +161,33 @@ class Life:
             names.append(os.path.join(directory or ".", _native.rank_file_name(r, self.nranks)))
         return names
 
+    # ------------------------------------------------------------- checkpoint
+    def save_checkpoint(self, directory: str) -> List[str]:
+        """Write one ``ckpt_rank<r>_of_<R>.npz`` per local slab: the packed words plus geometry and
+        the generation counter.  (The reference can only write its final world as text and cannot
+        read anything back, gol-main.c:135-139.)"""
+        os.makedirs(directory, exist_ok=True)
+        self.sync()
+        names = []
+        for i, r in enumerate(self.local_ranks):
+            path = os.path.join(directory, f"ckpt_rank{r}_of_{self.nranks}.npz")
+            np.savez_compressed(path, words=self.world.read_packed(i), width=self.width, rows=self.rows,
+                                rank=r, nranks=self.nranks, generation=self.generation)
+            names.append(path)
+        return names
+
+    def load_checkpoint(self, directory: str) -> "Life":
+        """Resume from :meth:`save_checkpoint` files (same geometry and rank count)."""
+        for i, r in enumerate(self.local_ranks):
+            path = os.path.join(directory, f"ckpt_rank{r}_of_{self.nranks}.npz")
+            with np.load(path) as z:
+                if (int(z["width"]), int(z["rows"]), int(z["nranks"]), int(z["rank"])) != \
+                        (self.width, self.rows, self.nranks, r):
+                    raise _native.GolError(f"{path} was written for a different geometry")
+                self.world.load_packed(i, np.ascontiguousarray(z["words"], dtype=np.uint64))
+                self.generation = int(z["generation"])
+        return self
+
     def report(self, seconds: float, iterations: int) -> str:
         """The two stdout lines of rank 0 (gol-main.c:124-125,132)."""
         return _native.format_report(seconds, self.nranks, self.width, self.rows, iterations)

@@ -61,3 +61,18 @@ def test_partial_cpu_world_refuses_plain_step():
     w = World(64, 8, nranks=2, first_rank=0, nlocal=1, backend="cpu")
     with pytest.raises(GolError, match="cpu_step_local"):
         w.step(1)
+
+
+def test_checkpoint_resume_round_trip(tmp_path):
+    a = Life(96, 20, ranks=3, backend="cpu").init(6, seed=8, density=0.4)
+    a.step(5)
+    a.save_checkpoint(str(tmp_path))
+    a.step(7)
+    b = Life(96, 20, ranks=3, backend="cpu").load_checkpoint(str(tmp_path))
+    assert b.generation == 5
+    b.step(7)
+    assert (a.all_local_cells() == b.all_local_cells()).all()
+    from gol_b200 import GolError
+
+    with pytest.raises(GolError, match="different geometry"):
+        Life(96, 21, ranks=3, backend="cpu").load_checkpoint(str(tmp_path))

@@ -226,3 +226,33 @@ def test_native_cli_on_gpu(tmp_path):
     r = subprocess.run([exe, "4", "64", "16", "256", "1", "--check", "--ranks", "2", "--devices", "1",
                         "--outdir", str(tmp_path)], capture_output=True, text=True)
     assert r.returncode == 0 and "CHECK: OK" in r.stdout, r.stdout + r.stderr
+
+
+def test_checkpoint_resume_on_gpu(tmp_path):
+    a = Life(512, 64, ranks=2).init(6, seed=2)
+    a.step(9)
+    a.save_checkpoint(str(tmp_path))
+    a.step(11).sync()
+    b = Life(512, 64, ranks=2).load_checkpoint(str(tmp_path))
+    b.step(11).sync()
+    assert (a.all_local_cells() == b.all_local_cells()).all()
+    a.close()
+    b.close()
+
+
+def test_watchdog_reports_a_dead_neighbour(monkeypatch):
+    """Failure detection: a rank whose neighbour never sends must not hang the GPU.  World `a`
+    owns rank 0 of 2; its neighbour is wired to an idle world `b` in the same process, so the
+    halo words `a` waits for never arrive.  The flag wait gives up after GOL_WATCHDOG_MS and
+    sync() reports which side timed out."""
+    monkeypatch.setenv("GOL_WATCHDOG_MS", "300")
+    a = World(256, 32, nranks=2, first_rank=0, nlocal=1, backend="cuda", ndevices=1)
+    b = World(256, 32, nranks=2, first_rank=1, nlocal=1, backend="cuda", ndevices=1)
+    a.import_blob(1, b.export_blob(0))
+    a.connect()
+    a.init_pattern(6)
+    a.step(4)
+    with pytest.raises(GolError, match="did not arrive within the watchdog"):
+        a.sync()
+    a.close()
+    b.close()
