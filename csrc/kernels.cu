@@ -60,10 +60,10 @@ __device__ __noinline__ void wait_words(SlabState* st, int side, unsigned long l
   if (ld_acquire_sys(f) >= target) return;
   const unsigned long long t0 = globaltimer_ns();
   const unsigned long long limit = st->watchdog_ns;
-  unsigned ns = 20;
+  unsigned ns = 0;   // poll back to back first: the data is usually a few hundred ns away
   while (ld_acquire_sys(f) < target) {
-    __nanosleep(ns);
-    if (ns < 640) ns <<= 1;
+    if (ns) __nanosleep(ns);
+    ns = ns < 8 ? ns + 1 : (ns < 640 ? ns << 1 : ns);
     if (globaltimer_ns() - t0 > limit) {
       atomicExch(&st->error, 1 + side);
       return;
@@ -227,12 +227,18 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
   const uint64_t* bot_col = c.rbot + g.wi - c.H * c.stride;                // row y (>=H) at bot_col + y*stride
   uint64_t* out_col = c.out + g.wi;
   const uint32_t m2 = c.m2, m31 = c.m31;
+  const bool fresh = c.consume != 0;
+  // halo push straight from the registers that hold the new row (EDGE tasks only): the peer
+  // store leaves as soon as the row exists and its NVLink latency overlaps the rest of the strip
+  uint64_t* ptop_col = c.ptop + g.wi;                                // row y at ptop_col + y*stride
+  uint64_t* pbot_col = c.pbot + g.wi - (c.H - c.push) * c.stride;    // row y at pbot_col + y*stride
+  const int64_t push_lo = c.push, push_hi = c.H - c.push;
 
   auto load_row = [&](int i) -> uint64_t {
     i = i < last ? i : last;  // rows past the end are re-reads of the last row (never stored)
     const int64_t y = y_in + i;
     const uint64_t* p = in_col + y * c.stride;
-    if (EDGE) {
+    if (EDGE && fresh) {
       p = (y < 0) ? top_col + y * c.stride : p;
       p = (y >= c.H) ? bot_col + y * c.stride : p;
     }
@@ -274,7 +280,13 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
     for (int j = 0; j < B; ++j) {
       const uint64_t o = push_row<K, V>(s, cur[j], K, m2, m31);
       const int64_t y = yb + j;
-      if (g.owner && y < g.y1) st_cg(out_col + y * c.stride, o);
+      if (g.owner && y < g.y1) {
+        st_cg(out_col + y * c.stride, o);
+        if (EDGE && c.push) {
+          if (y >= 0 && y < push_lo) st_cg(ptop_col + y * c.stride, o);
+          if (y >= push_hi && y < c.H) st_cg(pbot_col + y * c.stride, o);
+        }
+      }
     }
   }
 }
@@ -293,23 +305,24 @@ __device__ __forceinline__ TaskGeom make_geom(const PassCtx& c, int64_t y0, int6
   return g;
 }
 
-// Halo push (fused MPI_Isend, gol-main.c:104-107): the rows this task just produced that the
-// ring neighbours need go straight into their recv buffers, then the word count is published.
-__device__ __forceinline__ void push_edges(SlabState* st, const PassCtx& c, const TaskGeom& g, int lane) {
-  if (!c.push) return;
-  const int64_t t0 = g.y0 > 0 ? g.y0 : 0;
-  const int64_t t1 = g.y1 < c.push ? g.y1 : c.push;              // rows [0, push) -> prev
-  const int64_t b0 = g.y0 > c.H - c.push ? g.y0 : c.H - c.push;  // rows [H-push, H) -> next
-  const int64_t b1 = g.y1 < c.H ? g.y1 : c.H;
-  const int rows_top = t1 > t0 ? (int)(t1 - t0) : 0;
-  const int rows_bot = b1 > b0 ? (int)(b1 - b0) : 0;
+// Rows of [y0, y1) that the ring neighbours need: [0, push) -> prev, [H-push, H) -> next.
+__device__ __forceinline__ void push_ranges(const PassCtx& c, int64_t y0, int64_t y1, int* rows_top,
+                                            int* rows_bot) {
+  const int64_t t0 = y0 > 0 ? y0 : 0;
+  const int64_t t1 = y1 < c.push ? y1 : c.push;
+  const int64_t b0 = y0 > c.H - c.push ? y0 : c.H - c.push;
+  const int64_t b1 = y1 < c.H ? y1 : c.H;
+  *rows_top = (c.push && t1 > t0) ? (int)(t1 - t0) : 0;
+  *rows_bot = (c.push && b1 > b0) ? (int)(b1 - b0) : 0;
+}
+
+// Halo publish (the completion half of the fused MPI_Isend, gol-main.c:104-107): the edge rows
+// were stored into the neighbours' recv buffers as they were produced (stream_rows<EDGE>); here
+// the word count is published.
+__device__ __forceinline__ void publish_edges(SlabState* st, const PassCtx& c, const TaskGeom& g, int lane) {
+  int rows_top, rows_bot;
+  push_ranges(c, g.y0, g.y1, &rows_top, &rows_bot);
   if (rows_top | rows_bot) {
-    if (g.owner) {
-      const uint64_t* mine = c.out + g.wi;
-      for (int64_t y = t0; y < t1; ++y) st_cg(c.ptop + y * c.stride + g.wi, ld_cg(mine + y * c.stride));
-      for (int64_t y = b0; y < b1; ++y)
-        st_cg(c.pbot + (y - (c.H - c.push)) * c.stride + g.wi, ld_cg(mine + y * c.stride));
-    }
     // No per-lane fence: the warp barrier orders every lane's stores before lane 0's
     // red.release.sys, and a release is cumulative over what happens-before it.  (A per-lane
     // __threadfence_system() is a fence.sc.sys; it kept the edge warp, and with it the kernel,
@@ -330,17 +343,21 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int6
   const TaskGeom g = make_geom(c, y0, y1, cg, lane);
   const bool reads_top = c.consume && (g.y0 - K < 0);
   const bool reads_bot = c.consume && (g.y1 + K > c.H);
+  int rows_top, rows_bot;
+  push_ranges(c, g.y0, g.y1, &rows_top, &rows_bot);
   if (reads_top || reads_bot) {
     if (lane == 0) {
       if (reads_top) wait_words(st, 0, c.target);
       if (reads_bot) wait_words(st, 1, c.target);
     }
     __syncwarp();
-    stream_rows<K, V, true>(c, g);
+  }
+  if (reads_top || reads_bot || rows_top || rows_bot) {
+    stream_rows<K, V, true>(c, g);    // recv-row sources and inline halo push
+    publish_edges(st, c, g, lane);
   } else {
     stream_rows<K, V, false>(c, g);
   }
-  push_edges(st, c, g, lane);
 }
 
 // Last CTA of a launch advances the slab's counters.
@@ -477,7 +494,9 @@ __global__ void __launch_bounds__(NW * 32, 512 / (NW * 32))
   int64_t y0, y1;
   strip_range(order, p.nstrips, -(int64_t)ext_out, c.H + ext_out, p.strip_rows, p.edge_rows, &y0, &y1);
   const int cg = c4 * kWarps + warp;
-  const bool edge = c.consume && (y0 - K < 0 || y1 + K > c.H);
+  int rows_top, rows_bot;
+  push_ranges(c, y0, y1, &rows_top, &rows_bot);
+  const bool edge = (c.consume && (y0 - K < 0 || y1 + K > c.H)) || rows_top || rows_bot;
 
   if (edge) {
     if (cg < p.col_groups) fused_task<K, 0>(st, c, y0, y1, cg, lane);
@@ -567,7 +586,6 @@ __global__ void __launch_bounds__(NW * 32, 512 / (NW * 32))
         }
       }
     }
-    if (cg < p.col_groups) push_edges(st, c, g, lane);
   }
   finish_pass(st, p, gridDim.x);
 }

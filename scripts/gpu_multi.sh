@@ -1,6 +1,6 @@
 mkdir -p gpurun_out
 N=$(nvidia-smi -L | wc -l)
-timeout 600 python -m pytest tests/test_gpu_multi.py -m gpu -x -q > gpurun_out/pytest_multi.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_multi.log
+timeout 600 python -m pytest tests/test_gpu_multi.py -m gpu -x -q -k "process_per_gpu" > gpurun_out/pytest_multi.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_multi.log
 tail -3 gpurun_out/pytest_multi.log
 OUT=gpurun_out/multi_$N.log; : > $OUT
 tr() { local n=$1; shift; echo "# n=$n $*" >> $OUT
