@@ -1007,7 +1007,13 @@ int gol_world_step(gol_world_t* w, int64_t gens) {
   }
   if (!w->connected) return set_error(GOL_ERR_STATE, "gol_world_connect has not been called");
   nvtxRangePushA("gol_world_step");
-  const int rc = step_cuda(w, gens);
+  // Long runs are cut into chunks of at most 4096 exchange periods so that a captured graph
+  // stays small (a few thousand kernel nodes) however many generations are asked for; the
+  // chunk graph is cached and replayed.
+  const int64_t chunk = (int64_t)std::max(1, w->plan.exchange_depth) * 4096;
+  int rc = GOL_OK;
+  for (int64_t done = 0; done < gens && rc == GOL_OK; done += chunk)
+    rc = step_cuda(w, std::min(chunk, gens - done));
   nvtxRangePop();
   return rc;
 }
@@ -1048,7 +1054,9 @@ int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms) {
     return rc;
   }
   if (!w->connected) return set_error(GOL_ERR_STATE, "gol_world_connect has not been called");
-  int rc = step_cuda(w, gens, /*launch=*/false);  // graphs built outside the timed region
+  const int64_t chunk = (int64_t)std::max(1, w->plan.exchange_depth) * 4096;
+  int rc = step_cuda(w, std::min(chunk, gens), /*launch=*/false);  // graphs built outside the timed region
+  if (rc == GOL_OK && gens > chunk && gens % chunk) rc = step_cuda(w, gens % chunk, /*launch=*/false);
   if (rc) return rc;
   for (auto& g : w->groups) {
     CU_TRY(cudaSetDevice(g.device));

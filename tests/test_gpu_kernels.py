@@ -256,3 +256,9 @@ def test_watchdog_reports_a_dead_neighbour(monkeypatch):
         a.sync()
     a.close()
     b.close()
+
+
+def test_long_run_is_cut_into_graph_chunks():
+    # step() replays a cached graph per chunk of 4096 exchange periods; 4096 + 37 crosses one cut
+    got, _ = run_gpu(6, 64, 16, 2, 4096 + 37, mode="fused", k=1, seed=12)
+    assert (got == expected(6, 64, 16, 2, 4096 + 37, seed=12)).all()
