@@ -77,3 +77,15 @@ def test_python_cli_usage():
 
     assert cli.main(["1", "2"]) == 255
     assert cli.main(["8", "32", "2", "512", "0"]) == 255
+
+
+def test_rank_file_reader_round_trip(tmp_path):
+    from gol_b200.utils.io import read_rank_file, read_world
+
+    rng = np.random.default_rng(1)
+    world = (rng.random((12, 9)) < 0.5).astype(np.uint8)
+    for r in range(3):
+        n.write_rank_file(str(tmp_path / n.rank_file_name(r, 3)), world[4 * r:4 * r + 4], r)
+    rank, first, cells = read_rank_file(str(tmp_path / "Rank_2_of_3.txt"))
+    assert (rank, first) == (2, 8) and (cells == world[8:]).all()
+    assert (read_world(str(tmp_path), 3) == world).all()
