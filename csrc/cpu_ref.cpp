@@ -114,7 +114,7 @@ int gol_pack_bytes(const uint8_t* cells, uint64_t* words, int64_t W, int64_t H) 
     uint64_t* row = words + y * st;
     for (int64_t w = 0; w < st; ++w) row[w] = 0;
     for (int64_t x = 0; x < W; ++x)
-      if (cells[(size_t)(y * W + x)]) row[x >> 6] |= 1ull << (x & 63);
+      if (cells[(size_t)(y * W + x)]) row[x >> 6] |= 1ull << bitpos((int)(x & 63));
   }
   return GOL_OK;
 }
@@ -124,7 +124,7 @@ int gol_unpack_words(const uint64_t* words, uint8_t* cells, int64_t W, int64_t H
   const int64_t st = row_stride_words(W);
   for (int64_t y = 0; y < H; ++y)
     for (int64_t x = 0; x < W; ++x)
-      cells[(size_t)(y * W + x)] = (uint8_t)((words[y * st + (x >> 6)] >> (x & 63)) & 1ull);
+      cells[(size_t)(y * W + x)] = (uint8_t)col_bit(words + y * st, x);
   return GOL_OK;
 }
 

@@ -112,7 +112,8 @@ __device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long l
 
 // ---- the bit-sliced generation stage, spelled out in 32-bit LOP3s -----------------------------
 // Each lane owns one 64-cell word as two 32-bit halves.  Per half and per generation:
-//   2 SHF (funnel shifts bring in the x-neighbour bit, across lanes via SHFL)
+//   1 SHF (funnel shift brings in the x-neighbour bit, across lanes via SHFL; the other
+//   neighbour is the other half at the same bit index thanks to the even/odd layout)
 //   2 LOP3 horizontal sum, 4 LOP3 vertical carry-save, 4 LOP3 rule decode  = 10 LOP3
 // The LUTs are written out so that ptxas cannot pick a longer decomposition.
 template <int LUT>
@@ -120,15 +121,6 @@ __device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
   uint32_t r;
   asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
   return r;
-}
-
-// a * b + {c_hi:c_lo} as one IMAD.WIDE (the 64-bit addend rides along for free)
-__device__ __forceinline__ uint64_t mad_wide(uint32_t a, uint32_t b, uint32_t c_lo, uint32_t c_hi) {
-  uint64_t d;
-  asm("{\n\t.reg .b64 c;\n\tmov.b64 c, {%3, %4};\n\tmad.wide.u32 %0, %1, %2, c;\n\t}"
-      : "=l"(d)
-      : "r"(a), "r"(b), "r"(c_lo), "r"(c_hi));
-  return d;
 }
 
 struct Half {
@@ -164,10 +156,8 @@ __device__ __forceinline__ uint32_t stage_half(Half& s, uint32_t h0, uint32_t h1
 // returned at step i (i >= 2K, nst == K) is generation +K of row y_in + i - K.  nst < K is used
 // while the pipeline fills: stage t has no valid input before step 2t, so running it is waste.
 //
-// V selects how the x-neighbour words are formed:
-//   V = 0  funnel shifts (SHF, ALU pipe): 4 per word
-//   V = 1  integer multiply-adds (IMAD / IMAD.WIDE / IMAD.HI, FMA pipe) by 2 and 2^31 held in
-//          registers, which moves the shifts off the pipe that the LOP3s saturate
+// (V is kept as a template slot for kernel variants; only V = 0 exists.  A shift-by-multiply
+// variant that moved the funnel shifts to the FMA pipe measured slower and was removed.)
 template <int K, int V>
 __device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64, int nst, uint32_t m2,
                                              uint32_t m31) {
@@ -175,27 +165,16 @@ __device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64, int ns
 #pragma unroll
   for (int t = 0; t < K; ++t) {
     if (t < nst) {
-      uint32_t Llo, Lhi, Rlo, Rhi;
-      if (V == 0) {
-        const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);    // left lane's top half: carries bit 63
-        const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);  // right lane's low half: carries bit 0
-        Llo = __funnelshift_l(lhi, lo, 1);
-        Lhi = __funnelshift_l(lo, hi, 1);
-        Rlo = __funnelshift_r(lo, hi, 1);
-        Rhi = __funnelshift_r(hi, rlo, 1);
-      } else {
-        // sender side: my bit 63 as a 0/1 value, my bit 0 moved to bit 31
-        const uint32_t cin = __shfl_up_sync(kFull, __umulhi(hi, m2), 1);
-        const uint32_t rin = __shfl_down_sync(kFull, lo * m31, 1);
-        // {hi:lo} * 2 + carry-in: lo*2 is 33 bits wide, its bit 32 lands in the high word
-        const uint64_t L = mad_wide(lo, m2, cin, hi * m2);
-        // {hi:lo} / 2 + carry-in: hi * 2^31 = {hi >> 1 : hi << 31}
-        const uint64_t R = mad_wide(hi, m31, __umulhi(lo, m31), rin);
-        Llo = (uint32_t)L;
-        Lhi = (uint32_t)(L >> 32);
-        Rlo = (uint32_t)R;
-        Rhi = (uint32_t)(R >> 32);
-      }
+      // lo = even columns, hi = odd columns of my 64 cells (life_math.h layout).  The left
+      // neighbour of an even column is the previous odd column (shift in the left lane's last
+      // odd column); its right neighbour is the odd column at the SAME bit index - no shift.
+      // Symmetrically for odd columns.  One funnel shift per half instead of two.
+      const uint32_t lhi = __shfl_up_sync(kFull, hi, 1);    // left lane's odd columns: its bit 31 is my column -1
+      const uint32_t rlo = __shfl_down_sync(kFull, lo, 1);  // right lane's even columns: its bit 0 is my column 64
+      const uint32_t Llo = __funnelshift_l(lhi, hi, 1);     // (hi << 1) | (lhi >> 31)
+      const uint32_t Rlo = hi;
+      const uint32_t Lhi = lo;
+      const uint32_t Rhi = __funnelshift_r(lo, rlo, 1);     // (lo >> 1) | (rlo << 31)
       const uint32_t h0lo = lop3<0x96>(Llo, lo, Rlo), h1lo = lop3<0xE8>(Llo, lo, Rlo);
       const uint32_t h0hi = lop3<0x96>(Lhi, hi, Rhi), h1hi = lop3<0xE8>(Lhi, hi, Rhi);
       const uint32_t olo = stage_half(s[t].lo, h0lo, h1lo, lo);
@@ -834,7 +813,7 @@ __global__ void pack_kernel(const uint8_t* __restrict__ cells, uint64_t* __restr
     } else {
       for (int j = 0; j < n; ++j) v |= (uint64_t)(src[j] != 0) << j;
     }
-    words[y * stride + w] = v;
+    words[y * stride + w] = std_to_il(v);   // column order -> storage layout
   }
 }
 
@@ -846,7 +825,7 @@ __global__ void unpack_kernel(const uint64_t* __restrict__ words, uint8_t* __res
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t y = i / ws, w = i - y * ws;
-    const uint64_t v = words[y * stride + w];
+    const uint64_t v = il_to_std(words[y * stride + w]);   // storage layout -> column order
     uint8_t* dst = cells + y * W + w * 64;
     const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
     if (aligned && n == 64) {
@@ -907,7 +886,7 @@ __global__ void format_rows_kernel(const uint64_t* __restrict__ rows, int64_t st
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / ws, w = i - r * ws;
-    const uint64_t v = rows[r * stride + w];
+    const uint64_t v = il_to_std(rows[r * stride + w]);   // storage layout -> column order
     char* row_text = text + r * pitch;
     char* dst = row_text + kTextCellOff + w * 128;
     const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
@@ -1009,16 +988,6 @@ static uint64_t g_launches = 0;
 void count_launch(uint64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }
 uint64_t launch_count_value() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
-// GOL_FUSED_VARIANT=1 selects the shift-by-multiply instantiation (K = 4 only).
-static int fused_variant() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("GOL_FUSED_VARIANT");
-    v = e ? atoi(e) : 0;
-  }
-  return v;
-}
-
 // GOL_PDL=1: launch fused passes with programmatic dependent launch.
 static bool pdl_enabled() {
   static int v = -1;
@@ -1067,7 +1036,6 @@ cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParam
                          cudaStream_t s) {
   const void* fn = nullptr;
   GOL_DISPATCH_K(K, fn = fused_fn<KK>());
-  if (fused_variant() == 1 && K == 4) fn = fused_fn<4, 1>();
   if (!fn) return cudaErrorInvalidValue;
   const int wpb = threads / 32;
   const int ntasks = p.nstrips * p.col_groups;

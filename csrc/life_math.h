@@ -1,6 +1,10 @@
 // life_math.h — bit-sliced Conway B3/S23 arithmetic shared by host and device.
 //
-// One machine word holds 64 (or 32) cells of one row, LSB = lowest column.
+// One 64-bit word holds 64 consecutive cells of one row, EVEN/ODD INTERLEAVED: the low 32 bits
+// are the even columns of the block, the high 32 bits the odd columns (column 64w + j lives at
+// bit (j >> 1) + 32 * (j & 1)).  With this layout one of the two x-neighbours of every cell sits
+// at the same bit index of the other half, so a generation needs one funnel shift per 32 cells
+// instead of two (22 instead of 24 integer-pipe instructions per 64 cells).
 // The same functions drive the CPU packed stepper, the CUDA kernels and the
 // pattern initialisers, so a CPU test of this header is a test of the device
 // math too.
@@ -49,6 +53,34 @@ template <class T> GOL_HD T life_rule(HSum<T> a, HSum<T> b, HSum<T> d, T centre)
   const T eq4hi = ~(k0 ^ t1) & (k1 ^ k0);      // bit1 = 0, bit2 = 1, bit3 = 0
   return (t0 & eq3hi) | (~t0 & centre & eq4hi);
 }
+
+// ---- word layout -------------------------------------------------------------
+// bit index of local column j (0..63) inside its word
+GOL_HD int bitpos(int j) { return (j >> 1) + ((j & 1) << 5); }
+
+// 32 bits -> the even bit positions of 64 bits
+GOL_HD uint64_t spread32(uint64_t x) {
+  x &= 0xffffffffull;
+  x = (x | (x << 16)) & 0x0000ffff0000ffffull;
+  x = (x | (x << 8)) & 0x00ff00ff00ff00ffull;
+  x = (x | (x << 4)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | (x << 2)) & 0x3333333333333333ull;
+  x = (x | (x << 1)) & 0x5555555555555555ull;
+  return x;
+}
+// the even bit positions of 64 bits -> 32 bits
+GOL_HD uint64_t compact32(uint64_t x) {
+  x &= 0x5555555555555555ull;
+  x = (x | (x >> 1)) & 0x3333333333333333ull;
+  x = (x | (x >> 2)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | (x >> 4)) & 0x00ff00ff00ff00ffull;
+  x = (x | (x >> 8)) & 0x0000ffff0000ffffull;
+  x = (x | (x >> 16)) & 0x00000000ffffffffull;
+  return x;
+}
+// column-ordered word (bit j = column j) <-> interleaved storage word
+GOL_HD uint64_t std_to_il(uint64_t x) { return compact32(x) | (compact32(x >> 1) << 32); }
+GOL_HD uint64_t il_to_std(uint64_t x) { return spread32(x) | (spread32(x >> 32) << 1); }
 
 // ---- counter-based hash for the random-density pattern --------------------
 GOL_HD uint64_t mix64(uint64_t z) {
@@ -123,7 +155,7 @@ GOL_HD uint64_t pattern_word(const PatternArgs& a, int64_t y, int64_t w) {
   const int64_t x0 = w * 64;
   for (int j = 0; j < 64; ++j) {
     const int64_t x = x0 + j;
-    if (x < a.W && pattern_cell(a, y, x)) v |= (1ull << j);
+    if (x < a.W && pattern_cell(a, y, x)) v |= (1ull << bitpos(j));
   }
   return v;
 }
@@ -132,27 +164,39 @@ GOL_HD int64_t words_per_row(int64_t W) { return (W + 63) / 64; }
 // Row stride in words: 16-byte aligned rows (TMA / 128-bit access friendly).
 GOL_HD int64_t row_stride_words(int64_t W) { return (words_per_row(W) + 1) & ~int64_t(1); }
 GOL_HD uint64_t tail_mask(int64_t W) {
-  const int t = (int)(W & 63);
-  return t ? ((1ull << t) - 1) : ~0ull;
+  const int t = (int)(W & 63);  // valid columns in the last word
+  if (!t) return ~0ull;
+  const uint64_t even = (1ull << ((t + 1) >> 1)) - 1, odd = (1ull << (t >> 1)) - 1;
+  return even | (odd << 32);
+}
+GOL_HD uint64_t col_bit(const uint64_t* row, int64_t x) {
+  return (row[x >> 6] >> bitpos((int)(x & 63))) & 1ull;
 }
 
 // ---- x-neighbour words with torus wrap, any W (W % 64 may be non-zero) -----
-// left_of: bit j = cell at column 64w + j - 1;  right_of: bit j = column 64w + j + 1.
-// Rows must have zero bits beyond column W-1.
+// left_of: the word whose cell at column c is the cell at column c-1; right_of: column c+1.
+// Rows must have zero bits beyond column W-1.  With A = even columns (low half) and B = odd
+// columns (high half):  left = {(B << 1) | carry, A},  right = {B, (A >> 1) | carry << 31}.
 GOL_HD uint64_t left_of(const uint64_t* row, int64_t w, int64_t W) {
-  uint64_t carry;
-  if (w > 0) {
-    carry = row[w - 1] >> 63;
-  } else {
-    const int64_t last = W - 1;
-    carry = (row[last >> 6] >> (last & 63)) & 1ull;
-  }
-  return (row[w] << 1) | carry;
+  const uint64_t A = row[w] & 0xffffffffull, B = row[w] >> 32;
+  // column 64w - 1: the previous word's last odd column (bit 63), or column W-1 across the seam
+  const uint64_t carry = (w > 0) ? (row[w - 1] >> 63) : col_bit(row, W - 1);
+  const uint64_t LA = ((B << 1) | carry) & 0xffffffffull;
+  return LA | (A << 32);
 }
 GOL_HD uint64_t right_of(const uint64_t* row, int64_t w, int64_t ws, int64_t W) {
-  if (w < ws - 1) return (row[w] >> 1) | (row[w + 1] << 63);
-  const int t = (int)((W - 1) & 63);  // bit index of column W-1 in the last word
-  return (row[w] >> 1) | ((row[0] & 1ull) << t);
+  const uint64_t A = row[w] & 0xffffffffull, B = row[w] >> 32;
+  uint64_t RA = B, RB = A >> 1;
+  if (w < ws - 1) {
+    RB |= (row[w + 1] & 1ull) << 31;  // column 64(w+1): the next word's first even column
+  } else {
+    // last word: the cell right of column W-1 is column 0
+    const int l = (int)((W - 1) & 63);
+    const uint64_t c0 = row[0] & 1ull;
+    if (l & 1) RB |= c0 << (l >> 1);
+    else RA |= c0 << (l >> 1);
+  }
+  return RA | (RB << 32);
 }
 
 // One output word of a single generation given the three source rows.

@@ -7,7 +7,10 @@
  *
  * Geometry (same as the reference, gol-main.c:22,76): rank r of R owns global
  * rows [r*H, (r+1)*H) of a W-wide, H*R-tall torus.  Cells are stored bit-packed,
- * 64 per uint64 word, bit j of word w of a row = column 64*w + j.
+ * 64 consecutive columns per uint64 word, even/odd interleaved: column 64*w + j of a row is
+ * bit (j >> 1) + 32 * (j & 1) of word w (even columns in the low half, odd columns in the
+ * high half; it saves one shift per 32 cells per generation).  gol_pack_bytes /
+ * gol_unpack_words / gol_cuda_pack / gol_cuda_unpack convert from and to byte cells.
  */
 #ifndef GOL_B200_H_
 #define GOL_B200_H_

@@ -73,10 +73,17 @@ def test_pack_unpack_round_trip_and_padding_is_zero():
         p = n.pack(g)
         assert p.shape == (6, n.row_stride_words(w))
         assert (n.unpack(p, w) == g).all()
-        full = int(p.view(np.uint64).sum(dtype=np.uint64)) if False else None
-        # bits beyond column w-1 must be zero
-        bits = np.unpackbits(p.view(np.uint8), bitorder="little").reshape(6, -1)
-        assert bits[:, w:].sum() == 0
+        # bits beyond column w-1 must be zero: the packed population equals the cell count
+        assert int(np.unpackbits(p.view(np.uint8)).sum()) == int(g.sum())
+
+
+def test_word_layout_is_even_odd_interleaved():
+    # column 64w + j lives at bit (j >> 1) + 32 * (j & 1): even columns low half, odd columns high half
+    for j in (0, 1, 2, 3, 62, 63):
+        g = np.zeros((1, 128), dtype=np.uint8)
+        g[0, 64 + j] = 1
+        p = n.pack(g)
+        assert int(p[0, 0]) == 0 and int(p[0, 1]) == 1 << ((j >> 1) + 32 * (j & 1))
 
 
 def test_reference_quirk_model_matches_survey_table():
