@@ -69,9 +69,7 @@ struct PassParams {
   int32_t nstrips;
   int32_t edge_rows;  // > 0: the first / last edge_rows output rows are strips of their own (scheduled
                       // first and short, so the halo push leaves early and overlaps the interior)
-  uint32_t mul2, mul31;  // 2 and 2^31, passed as data so the shift-by-multiply variant keeps its IMADs
   int32_t tma_rank;      // TMA mode: 2 = {ws, rows} map, 3 = {16, ws/16, rows} map (128-byte inner box)
-  int32_t pad2;
 };
 
 // ---- strip decomposition of one pass (shared by host planner and kernels) ----------------

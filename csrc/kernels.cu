@@ -82,16 +82,12 @@ struct PassCtx {
   unsigned long long target;
   int64_t H, ws, stride;
   int ext_in, consume, push;
-  uint32_t m2, m31;       // 2 and 2^31 as run-time values (shift-by-multiply variant)
 };
 
 __device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long long pass,
                                             unsigned long long exch, unsigned long long words_seen,
-                                            int ext_in, int consume, int push,
-                                            uint32_t m2 = 2u, uint32_t m31 = 0x80000000u) {
+                                            int ext_in, int consume, int push) {
   PassCtx c;
-  c.m2 = m2;
-  c.m31 = m31;
   const int64_t stride = st->stride;
   c.in = st->buf[pass & 1] + (int64_t)st->G * stride;
   c.out = st->buf[(pass + 1) & 1] + (int64_t)st->G * stride;
@@ -159,8 +155,7 @@ __device__ __forceinline__ uint32_t stage_half(Half& s, uint32_t h0, uint32_t h1
 // (V is kept as a template slot for kernel variants; only V = 0 exists.  A shift-by-multiply
 // variant that moved the funnel shifts to the FMA pipe measured slower and was removed.)
 template <int K, int V>
-__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64, int nst, uint32_t m2,
-                                             uint32_t m31) {
+__device__ __forceinline__ uint64_t push_row(Stage (&s)[K], uint64_t x64, int nst) {
   uint32_t lo = (uint32_t)x64, hi = (uint32_t)(x64 >> 32);
 #pragma unroll
   for (int t = 0; t < K; ++t) {
@@ -205,7 +200,6 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
   const uint64_t* top_col = c.rtop + g.wi + (int64_t)c.ext_in * c.stride;  // row y (<0) at top_col + y*stride
   const uint64_t* bot_col = c.rbot + g.wi - c.H * c.stride;                // row y (>=H) at bot_col + y*stride
   uint64_t* out_col = c.out + g.wi;
-  const uint32_t m2 = c.m2, m31 = c.m31;
   const bool fresh = c.consume != 0;
   // halo push straight from the registers that hold the new row (EDGE tasks only): the peer
   // store leaves as soon as the row exists and its NVLink latency overlaps the rest of the strip
@@ -237,9 +231,9 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
 #pragma unroll
     for (int i = 0; i < 2 * K; ++i) pre[i] = load_row(i);
 #pragma unroll
-    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, pre[i], (i / 2 + 1 < K) ? i / 2 + 1 : K, m2, m31);
+    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, pre[i], (i / 2 + 1 < K) ? i / 2 + 1 : K);
   } else {
-    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, load_row(i), K, m2, m31);
+    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, load_row(i), K);
   }
 
   // steady state: every row in yields one row out
@@ -257,7 +251,7 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
     const int64_t yb = g.y0 + (int64_t)b * B;
 #pragma unroll
     for (int j = 0; j < B; ++j) {
-      const uint64_t o = push_row<K, V>(s, cur[j], K, m2, m31);
+      const uint64_t o = push_row<K, V>(s, cur[j], K);
       const int64_t y = yb + j;
       if (g.owner && y < g.y1) {
         st_cg(out_col + y * c.stride, o);
@@ -373,8 +367,7 @@ __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* state
   const int task = blockIdx.x * wpb + (threadIdx.x >> 5);
   const int ntasks = p.nstrips * p.col_groups;
   if (task < ntasks) {
-    const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push,
-                               p.mul2, p.mul31);
+    const PassCtx c = make_ctx(st, st->pass, st->exch, st->words_seen, p.ext_in, p.consume, p.push);
     const int order = task / p.col_groups;
     const int cg = task - order * p.col_groups;
     const int ext_out = p.ext_in - K;
@@ -548,9 +541,9 @@ __global__ void __launch_bounds__(NW * 32, 512 / (NW * 32))
 #pragma unroll
         for (int r = 0; r < kChunk; ++r) {
           if (r < 2 * K) {
-            push_row<K, 0>(s, rows[r], (r / 2 + 1 < K) ? r / 2 + 1 : K, 2u, 0x80000000u);
+            push_row<K, 0>(s, rows[r], (r / 2 + 1 < K) ? r / 2 + 1 : K);
           } else {
-            const uint64_t o = push_row<K, 0>(s, rows[r], K, 2u, 0x80000000u);
+            const uint64_t o = push_row<K, 0>(s, rows[r], K);
             const int64_t y = y0 + (r - 2 * K);
             if (g.owner && y < y1) st_cg(out_col + y * c.stride, o);
           }
@@ -559,7 +552,7 @@ __global__ void __launch_bounds__(NW * 32, 512 / (NW * 32))
         const int64_t yb = y0 + (int64_t)ch * kChunk - 2 * K;
 #pragma unroll
         for (int r = 0; r < kChunk; ++r) {
-          const uint64_t o = push_row<K, 0>(s, rows[r], K, 2u, 0x80000000u);
+          const uint64_t o = push_row<K, 0>(s, rows[r], K);
           const int64_t y = yb + r;
           if (g.owner && y < y1) st_cg(out_col + y * c.stride, o);
         }
@@ -1041,8 +1034,6 @@ cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParam
   const int ntasks = p.nstrips * p.col_groups;
   dim3 grid((unsigned)((ntasks + wpb - 1) / wpb), (unsigned)nslabs);
   PassParams pp = p;
-  pp.mul2 = 2u;
-  pp.mul31 = 0x80000000u;
   void* args[] = {(void*)&d_states, (void*)&pp};
   count_launch(1);
   if (pdl_enabled()) {

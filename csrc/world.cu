@@ -608,6 +608,38 @@ void gol_world_destroy(gol_world_t* w) {
   delete w;
 }
 
+int gol_schedule_describe(const gol_config_t* cfg, int64_t gens, gol_pass_desc_t* out, int max_out,
+                          gol_plan_t* plan_out) {
+  if (!cfg || gens < 0 || (max_out > 0 && !out)) return set_error(GOL_ERR_ARG, "gol_schedule_describe: bad argument");
+  if (cfg->width < 1 || cfg->rows < 1) return set_error(GOL_ERR_ARG, "gol_schedule_describe: bad geometry");
+  gol_world tmp;  // never touches a device: only the planner and the schedule builder run
+  tmp.cfg = *cfg;
+  tmp.cfg.backend = GOL_BACKEND_CUDA;
+  tmp.W = cfg->width;
+  tmp.H = cfg->rows;
+  tmp.ws = words_per_row(tmp.W);
+  tmp.stride = row_stride_words(tmp.W);
+  tmp.cuda = true;
+  tmp.G = (int)std::min<int64_t>(GOL_MAX_GHOST, tmp.H);
+  int rc = make_plan(&tmp);
+  if (rc) return rc;
+  if (tmp.plan.strip_rows <= 0) tmp.plan.strip_rows = 64;  // the real value needs the device's occupancy
+  if (plan_out) *plan_out = tmp.plan;
+  const std::vector<PassItem> items = build_schedule(&tmp, gens);
+  for (size_t i = 0; i < items.size() && (int)i < max_out; ++i) {
+    gol_pass_desc_t& d = out[i];
+    memset(&d, 0, sizeof d);
+    d.prime = items[i].prime;
+    d.generic = items[i].generic;
+    d.prime_depth = items[i].depth;
+    d.k = items[i].p.k;
+    d.ext_in = items[i].p.ext_in;
+    d.consume = items[i].p.consume;
+    d.push = items[i].p.push;
+  }
+  return (int)items.size();
+}
+
 int gol_world_plan(const gol_world_t* w, gol_plan_t* out) {
   if (!w || !out) return set_error(GOL_ERR_ARG, "null argument");
   *out = w->plan;

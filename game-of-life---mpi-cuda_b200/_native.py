@@ -80,6 +80,7 @@ def _load() -> C.CDLL:
         "gol_world_create": (VP, [P(_Config)]),
         "gol_world_destroy": (None, [VP]),
         "gol_world_plan": (I32, [VP, P(_Plan)]),
+        "gol_schedule_describe": (I32, [P(_Config), I64, VP, I32, P(_Plan)]),
         "gol_world_export": (I32, [VP, I32, VP]),
         "gol_world_import": (I32, [VP, I32, VP]),
         "gol_world_connect": (I32, [VP]),
@@ -324,6 +325,27 @@ class World:
 
 
 # ---- thin functional wrappers over the CPU helpers -------------------------------------
+
+class _PassDesc(C.Structure):
+    _fields_ = [(n_, C.c_int32) for n_ in ("prime", "generic", "prime_depth", "k", "ext_in", "consume", "push",
+                                           "reserved")]
+
+
+def describe_schedule(width: int, rows: int, gens: int, mode: str = "auto", k: int = 0, depth: int = 0) -> dict:
+    """The launch sequence ``step(gens)`` runs for this geometry (no GPU needed): a list of dicts
+    (``prime`` / pass entries, see ``gol_pass_desc_t``) and the resolved plan."""
+    cfg = _Config()
+    cfg.width, cfg.rows, cfg.nranks, cfg.nlocal = int(width), int(rows), 1, 1
+    cfg.backend, cfg.mode, cfg.temporal_k, cfg.exchange_depth = BACKEND_CUDA, MODES[mode], int(k), int(depth)
+    plan = _Plan()
+    n_items = lib.gol_schedule_describe(C.byref(cfg), int(gens), None, 0, C.byref(plan))
+    if n_items < 0:
+        raise GolError(f"[{n_items}] {last_error()}")
+    buf = (_PassDesc * max(1, n_items))()
+    check(min(0, lib.gol_schedule_describe(C.byref(cfg), int(gens), buf, n_items, C.byref(plan))))
+    items = [{f: getattr(buf[i], f) for f, _ in _PassDesc._fields_ if f != "reserved"} for i in range(n_items)]
+    return {"items": items, "plan": {name: getattr(plan, name) for name, _ in _Plan._fields_}}
+
 
 def oracle_run(cells: np.ndarray, gens: int) -> np.ndarray:
     """True torus Life on a 2-D uint8 array (the test oracle; CPU, byte per cell)."""

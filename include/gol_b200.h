@@ -112,6 +112,18 @@ typedef struct gol_plan {
 } gol_plan_t;
 int gol_world_plan(const gol_world_t* w, gol_plan_t* out);
 
+/* The pass schedule step(gens) would run for a configuration, without touching a device
+ * (planner + schedule builder only).  One entry per kernel launch, in order: a halo prime
+ * (prime = 1, prime_depth rows pushed to each neighbour) or a pass of k generations whose
+ * input carries ext_in valid halo rows (consume = 1: they come fresh from the neighbours and
+ * are waited for) and which pushes `push` rows for the next exchange period.  Returns the
+ * number of entries (may exceed max_out) or a negative error.  Identical on every rank. */
+typedef struct gol_pass_desc {
+  int32_t prime, generic, prime_depth, k, ext_in, consume, push, reserved;
+} gol_pass_desc_t;
+int gol_schedule_describe(const gol_config_t* cfg, int64_t gens, gol_pass_desc_t* out, int max_out,
+                          gol_plan_t* plan_out);
+
 /* Multi-process wiring.  Each process exports one blob per local rank, all
  * ranks gather them (torch.distributed / any transport) and import the ones
  * they do not own; gol_world_connect() then resolves every local slab's ring
