@@ -11,7 +11,9 @@ HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${1:-/root/reference}"
 OUT="$HERE/_ref"
 mkdir -p "$OUT/src" "$OUT/bin" "$OUT/obj"
-cp "$REF/gol-main.c" "$REF/gol-with-cuda.cu" "$OUT/src/"
+if [ "$(cd "$REF" && pwd)" != "$(cd "$OUT/src" && pwd)" ]; then   # rebuild in place: sources already there
+  cp "$REF/gol-main.c" "$REF/gol-with-cuda.cu" "$OUT/src/"
+fi
 ( cd "$OUT/src" && sha256sum gol-main.c gol-with-cuda.cu > SHA256SUMS )
 ARCH="-gencode arch=compute_100,code=sm_100"
 gcc -O2 -c "$HERE/minimpi/minimpi.c" -o "$OUT/obj/minimpi.o"

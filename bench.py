@@ -86,7 +86,15 @@ def reference_measure(args) -> dict:
     the full 16384 x 16384 config and reported alongside.
     """
     bindir = os.path.join(ROOT, "baseline", "_ref", "bin")
-    if not all(os.path.exists(os.path.join(bindir, b)) for b in ("gol_ref", "gol_ref_noprintf", "mpirun")):
+    have = lambda: all(os.path.exists(os.path.join(bindir, b)) for b in ("gol_ref", "gol_ref_noprintf", "mpirun"))
+    if not have():
+        # binaries missing (fresh checkout): rebuild from the verbatim copies or from /root/reference
+        for src in (os.path.join(ROOT, "baseline", "_ref", "src"), "/root/reference"):
+            if os.path.exists(os.path.join(src, "gol-with-cuda.cu")):
+                subprocess.run(["bash", os.path.join(ROOT, "baseline", "build_ref.sh"), src],
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                break
+    if not have():
         return {"impl": "reference", "unavailable": "baseline/_ref/bin is missing: run baseline/build_ref.sh "
                 "(pip cannot install the reference: it has no setup.py/pyproject.toml)"}
     from gol_b200.utils.clocks import ClockSampler
