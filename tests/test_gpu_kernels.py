@@ -262,3 +262,27 @@ def test_long_run_is_cut_into_graph_chunks():
     # step() replays a cached graph per chunk of 4096 exchange periods; 4096 + 37 crosses one cut
     got, _ = run_gpu(6, 64, 16, 2, 4096 + 37, mode="fused", k=1, seed=12)
     assert (got == expected(6, 64, 16, 2, 4096 + 37, seed=12)).all()
+
+
+def test_slab_larger_than_2_pow_31_cells():
+    """The reference indexes cells with 32-bit ints and silently does nothing beyond 2^31 cells per
+    rank (gol-with-cuda.cu:198).  Here sizes are 64-bit: a 131072 x 32768 slab (2^32 cells, 512 MiB
+    per buffer) keeps the wrap-around blinker (pattern 4) and the glider (pattern 5) alive."""
+    W, H = 131072, 32768
+    w = World(W, H, nranks=1, backend="cuda")
+    w.connect()
+    w.init_pattern(4)
+    w.step(6)
+    w.sync()
+    assert w.population(0) == 3
+    row0 = w.read_packed(0)[0]
+    first, last = int(row0[0]), int(row0[W // 64 - 1])
+    assert first == (1 | (1 << 32)) and last == (1 << 63)      # columns 0, 1 and W-1 (interleaved layout)
+    w.init_pattern(5)
+    w.step(16)
+    w.sync()
+    assert w.population(0) == 5
+    w.init_pattern(6, 3, 0.5)
+    pop = w.population(0)
+    assert abs(pop / float(W * H) - 0.5) < 1e-3
+    w.close()
