@@ -170,6 +170,10 @@ def run_ours(args) -> int:
         return subprocess.call(cmd)
     torch.cuda.set_device(local_rank)
     distributed = world > 1
+    # nvidia-smi takes a second or two to start sampling: launch it before anything else
+    from gol_b200.utils.clocks import ClockSampler as _CS
+
+    sampler = _CS(gpu_index=local_rank, period_ms=50).start() if rank == 0 else None
     if distributed:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -199,8 +203,6 @@ def run_ours(args) -> int:
     host_words = torch.empty((rows, stride), dtype=torch.int64).pin_memory()
     nat.check(nat.lib.gol_world_read_packed(life.world._h, 0, host_words.data_ptr()))
     host_pop = torch.zeros(1, dtype=torch.int64).pin_memory()
-
-    sampler = ClockSampler(gpu_index=local_rank, period_ms=50).start() if rank == 0 else None
 
     for _ in range(args.warmup):
         life.step(gens)
@@ -235,7 +237,7 @@ def run_ours(args) -> int:
     barrier()
     e2e_s = time.perf_counter() - t0
     t_region1 = time.time()
-    clocks = sampler.stop() if sampler else {}
+    clocks = sampler.stop(t_region0, t_region1) if sampler else {}
 
     t = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if distributed:
@@ -262,7 +264,7 @@ def run_ours(args) -> int:
                        "threads_per_block": plan["threads_per_block"], "strip_rows": plan["strip_rows"],
                        "l2": "L2 flushed (256 MiB write) before every timed step; within a step the 64 MiB "
                              "double buffer is L2-resident by design"},
-            "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples")},
+            "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples", "scope")},
             "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": int(host_words.numel() * 8),
                     "d2h_bytes_per_step": 8, "ms_per_step": e2e_ms / args.steps,
                     "api": "Life.run_from_host(pinned_words, generations, pinned_result); Life.sync()"},

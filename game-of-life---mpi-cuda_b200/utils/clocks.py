@@ -5,6 +5,7 @@ import shutil
 import statistics
 import subprocess
 import threading
+import time
 from typing import Dict, List, Optional
 
 _QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -27,6 +28,7 @@ class ClockSampler:
                 continue
             try:
                 self.samples.append({
+                    "t": time.time(),
                     "index": int(parts[0]),
                     "sm": float(parts[1].split()[0]),
                     "max": float(parts[2].split()[0]),
@@ -48,7 +50,7 @@ class ClockSampler:
         self._thread.start()
         return self
 
-    def stop(self) -> Dict:
+    def stop(self, t0: Optional[float] = None, t1: Optional[float] = None) -> Dict:
         if self._proc is not None:
             self._proc.terminate()
             try:
@@ -57,19 +59,31 @@ class ClockSampler:
                 self._proc.kill()
             if self._thread is not None:
                 self._thread.join(timeout=2)
-        return self.summary()
+        return self.summary(t0, t1)
 
-    def summary(self) -> Dict:
+    def summary(self, t0: Optional[float] = None, t1: Optional[float] = None) -> Dict:
+        """Median SM clock, max clock and throttle reasons.  With a window [t0, t1] (time.time())
+        only the samples taken inside it count; if the window caught none (very short region) the
+        samples under load (highest power quartile) of the whole run are used and flagged."""
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        sm = [s["sm"] for s in self.samples]
-        reasons = sorted({r for s in self.samples for r in s["reasons"]})
+        chosen, scope = self.samples, "whole run"
+        if t0 is not None and t1 is not None:
+            inside = [s for s in self.samples if t0 <= s["t"] <= t1]
+            if inside:
+                chosen, scope = inside, "timed region"
+            else:
+                cut = sorted(s["power"] for s in self.samples)[(3 * len(self.samples)) // 4]
+                chosen, scope = [s for s in self.samples if s["power"] >= cut], "under load (region too short)"
+        sm = [s["sm"] for s in chosen]
+        reasons = sorted({r for s in chosen for r in s["reasons"]})
         return {
             "sm_mhz": statistics.median(sm),
-            "sm_max_mhz": max(s["max"] for s in self.samples),
-            "power_w_max": max(s["power"] for s in self.samples),
+            "sm_max_mhz": max(s["max"] for s in chosen),
+            "power_w_max": max(s["power"] for s in chosen),
             "reasons": reasons,
-            "samples": len(self.samples),
+            "samples": len(chosen),
+            "scope": scope,
         }
 
     def __enter__(self):
