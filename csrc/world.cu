@@ -63,6 +63,10 @@ struct Slab {
   std::vector<uint64_t> cbuf[2];
   std::vector<uint64_t> cghost[2];
   int ccur = 0;
+  // CPU executor of the GPU pass schedule (GOL_FLAG_CPU_SCHEDULE)
+  std::vector<uint64_t> ebuf[2];        // (H + 2G) rows with margins, like the device slab
+  std::vector<uint64_t> erecv[2][2];    // [side][exchange parity], G rows each
+  uint64_t epass = 0, eexch = 0;
 };
 
 struct PassItem {
@@ -160,7 +164,7 @@ int make_plan(gol_world* w) {
   int K = c.temporal_k > 0 ? c.temporal_k : 4;
   int depth = c.exchange_depth > 0 ? c.exchange_depth : K;
   const bool shape_ok = (w->W % 64) == 0;
-  if (!w->cuda) {
+  if (!w->cuda && !(c.flags & GOL_FLAG_CPU_SCHEDULE)) {
     p.mode = GOL_MODE_GENERIC;
     p.temporal_k = 1;
     p.exchange_depth = 1;
@@ -439,6 +443,94 @@ void cpu_step_slab(gol_world* w, Slab& s) {
   s.ccur ^= 1;
 }
 
+// ---- CPU executor of the GPU pass schedule -----------------------------------------
+// Runs exactly the launch sequence build_schedule() produces for the fused kernels - prime,
+// passes of k generations on inputs with ext_in valid halo rows, pushes into the neighbours'
+// double-buffered recv rows, in-slab margins for halos deeper than one pass - with the CPU
+// row stepper in place of the kernels.  It exists so that the schedule / halo-depth logic is
+// checked against the oracle without a GPU (tests/test_cpu_schedule.py).
+void cpu_sched_prime(gol_world* w, int depth) {
+  const int R = w->cfg.nranks;
+  const int64_t st = w->stride, H = w->H;
+  for (auto& s : w->slabs) {
+    Slab& prev = w->slabs[(size_t)((s.rank - 1 + R) % R)];
+    Slab& next = w->slabs[(size_t)((s.rank + 1) % R)];
+    const uint64_t* in = s.ebuf[s.epass & 1].data() + (int64_t)w->G * st;
+    // my first rows -> prev's bottom recv; my last rows -> next's top recv (parity of the next exchange)
+    std::copy(in, in + depth * st, prev.erecv[1][prev.eexch & 1].begin());
+    std::copy(in + (H - depth) * st, in + H * st, next.erecv[0][next.eexch & 1].begin());
+  }
+}
+
+void cpu_sched_pass(gol_world* w, const PassParams& p) {
+  const int R = w->cfg.nranks;
+  const int64_t st = w->stride, H = w->H;
+  const int ext_out = p.ext_in - p.k;
+  const int64_t n0 = H + 2 * p.ext_in;  // input rows, y in [-ext_in, H + ext_in)
+  std::vector<std::vector<uint64_t>> outs(w->slabs.size());
+  for (size_t si = 0; si < w->slabs.size(); ++si) {
+    Slab& s = w->slabs[si];
+    const uint64_t* in = s.ebuf[s.epass & 1].data() + (int64_t)w->G * st;
+    std::vector<uint64_t> a((size_t)(n0 * st)), b((size_t)(n0 * st));
+    for (int64_t i = 0; i < n0; ++i) {
+      const int64_t y = i - p.ext_in;
+      const uint64_t* src = in + y * st;
+      if (p.consume && y < 0) src = s.erecv[0][s.eexch & 1].data() + (y + p.ext_in) * st;
+      if (p.consume && y >= H) src = s.erecv[1][s.eexch & 1].data() + (y - H) * st;
+      std::copy(src, src + st, a.begin() + i * st);
+    }
+    // k generations on a shrinking window: after generation g rows [g, n0 - g) are valid
+    int64_t lo = 0, hi = n0;
+    for (int g = 0; g < p.k; ++g) {
+      const int64_t n = hi - lo - 2;
+      std::vector<const uint64_t*> in_rows((size_t)n + 2);
+      std::vector<uint64_t*> out_rows((size_t)n);
+      for (int64_t i = 0; i < n + 2; ++i) in_rows[(size_t)i] = a.data() + (lo + i) * st;
+      for (int64_t i = 0; i < n; ++i) out_rows[(size_t)i] = b.data() + (lo + 1 + i) * st;
+      cpu_step_rows(in_rows.data(), out_rows.data(), n, w->W);
+      a.swap(b);
+      ++lo;
+      --hi;
+    }
+    outs[si].assign(a.begin() + lo * st, a.begin() + hi * st);  // rows y in [-ext_out, H + ext_out)
+  }
+  for (size_t si = 0; si < w->slabs.size(); ++si) {
+    Slab& s = w->slabs[si];
+    uint64_t* out = s.ebuf[(s.epass + 1) & 1].data() + ((int64_t)w->G - ext_out) * st;
+    std::copy(outs[si].begin(), outs[si].end(), out);
+    if (p.push) {
+      Slab& prev = w->slabs[(size_t)((s.rank - 1 + R) % R)];
+      Slab& next = w->slabs[(size_t)((s.rank + 1) % R)];
+      const uint64_t* interior = outs[si].data() + (int64_t)ext_out * st;  // row 0
+      const uint64_t pe_prev = prev.eexch + (p.consume ? 1 : 0), pe_next = next.eexch + (p.consume ? 1 : 0);
+      std::copy(interior, interior + p.push * st, prev.erecv[1][pe_prev & 1].begin());
+      std::copy(interior + (H - p.push) * st, interior + H * st, next.erecv[0][pe_next & 1].begin());
+    }
+  }
+  for (auto& s : w->slabs) {
+    s.epass += 1;
+    if (p.consume) s.eexch += 1;
+  }
+}
+
+int cpu_run_schedule(gol_world* w, int64_t gens) {
+  const int64_t st = w->stride, H = w->H;
+  for (auto& s : w->slabs) {  // bring the I/O buffer into the margin-carrying slab
+    uint64_t* dst = s.ebuf[s.epass & 1].data() + (int64_t)w->G * st;
+    std::copy(s.cbuf[s.ccur].begin(), s.cbuf[s.ccur].begin() + H * st, dst);
+  }
+  const std::vector<PassItem> items = build_schedule(w, gens);
+  for (const PassItem& it : items) {
+    if (it.prime) cpu_sched_prime(w, it.depth);
+    else cpu_sched_pass(w, it.p);
+  }
+  for (auto& s : w->slabs) {
+    const uint64_t* src = s.ebuf[s.epass & 1].data() + (int64_t)w->G * st;
+    std::copy(src, src + H * st, s.cbuf[s.ccur].begin());
+  }
+  return GOL_OK;
+}
+
 }  // namespace
 }  // namespace gol
 
@@ -477,7 +569,13 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
     for (auto& s : w->slabs) {
       for (int b = 0; b < 2; ++b) s.cbuf[b].assign((size_t)(w->H * w->stride), 0);
       for (int b = 0; b < 2; ++b) s.cghost[b].assign((size_t)w->stride, 0);
+      if (cfg->flags & GOL_FLAG_CPU_SCHEDULE) {
+        for (int b = 0; b < 2; ++b) s.ebuf[b].assign((size_t)((w->H + 2 * w->G) * w->stride), 0);
+        for (int side = 0; side < 2; ++side)
+          for (int par = 0; par < 2; ++par) s.erecv[side][par].assign((size_t)(w->G * w->stride), 0);
+      }
     }
+    if ((cfg->flags & GOL_FLAG_CPU_SCHEDULE) && w->plan.strip_rows <= 0) w->plan.strip_rows = 64;
     w->connected = (cfg->nlocal == cfg->nranks);
     return w;
   }
@@ -1031,6 +1129,7 @@ int gol_world_step(gol_world_t* w, int64_t gens) {
       return set_error(GOL_ERR_STATE,
                        "CPU world owns %d of %d ranks: drive it with cpu_get_edge / cpu_set_ghost / cpu_step_local",
                        (int)w->slabs.size(), w->cfg.nranks);
+    if (w->cfg.flags & GOL_FLAG_CPU_SCHEDULE) return cpu_run_schedule(w, gens);
     for (int64_t g = 0; g < gens; ++g) {
       cpu_exchange_local(w);
       for (auto& s : w->slabs) cpu_step_slab(w, s);

@@ -100,6 +100,9 @@ typedef struct gol_config {
 
 #define GOL_FLAG_NO_GRAPH 1      /* launch passes one by one, no CUDA graph     */
 #define GOL_FLAG_NO_PEER_ACCESS 2 /* do not call cudaDeviceEnablePeerAccess     */
+#define GOL_FLAG_CPU_SCHEDULE 4   /* CPU backend: execute the GPU pass schedule (k, exchange
+                                     depth, margins, double-buffered recv rows) with the CPU
+                                     stepper, to check that logic without a GPU             */
 
 gol_world_t* gol_world_create(const gol_config_t* cfg);
 void gol_world_destroy(gol_world_t* w);
