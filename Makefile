@@ -36,7 +36,13 @@ sass: $(LIB)
 	@mkdir -p profiles/sass
 	cuobjdump -sass $(LIB) > profiles/sass/libgol_b200.sass
 
+test: all
+	python -m pytest tests -q -m "not gpu"
+
+test-gpu: all
+	python -m pytest tests -q -m gpu
+
 clean:
 	rm -rf $(OBJDIR) $(LIB) $(BIN)
 
-.PHONY: all clean sass
+.PHONY: all clean sass test test-gpu
