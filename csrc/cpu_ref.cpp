@@ -9,7 +9,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../include/gol_b200.h"
@@ -33,8 +35,8 @@ int set_error(int code, const char* fmt, ...) {
 // ---- packed CPU stepping of a block of rows --------------------------------
 // rows[-1] and rows[n] must be readable (ghost rows); all rows have `ws` valid
 // words and zero bits beyond W.  Torus wrap in x is done here.
-void cpu_step_rows(const uint64_t* const* in_rows, uint64_t* const* out_rows, int64_t nrows,
-                   int64_t W) {
+static void cpu_step_rows_serial(const uint64_t* const* in_rows, uint64_t* const* out_rows, int64_t nrows,
+                                 int64_t W) {
   // in_rows has nrows + 2 entries: [0] = row above the first, [nrows+1] = below the last.
   const int64_t ws = words_per_row(W);
   const uint64_t tm = tail_mask(W);
@@ -57,6 +59,29 @@ void cpu_step_rows(const uint64_t* const* in_rows, uint64_t* const* out_rows, in
       o[w] = v;
     }
   }
+}
+
+// Row blocks are independent within one generation, so large grids are split over host
+// threads (GOL_CPU_THREADS, default: hardware concurrency, capped at 16); each block reads
+// one extra row above and below, exactly like a rank's ghost rows.
+void cpu_step_rows(const uint64_t* const* in_rows, uint64_t* const* out_rows, int64_t nrows, int64_t W) {
+  static const int max_threads = [] {
+    const char* e = getenv("GOL_CPU_THREADS");
+    int n = e ? atoi(e) : (int)std::thread::hardware_concurrency();
+    return n < 1 ? 1 : (n > 16 ? 16 : n);
+  }();
+  const int64_t work = nrows * words_per_row(W);
+  int nt = (int)std::min<int64_t>(max_threads, nrows / 16);
+  if (work < (1 << 16) || nt < 2) {
+    cpu_step_rows_serial(in_rows, out_rows, nrows, W);
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nt; ++t) {
+    const int64_t y0 = nrows * t / nt, y1 = nrows * (t + 1) / nt;
+    pool.emplace_back([=] { cpu_step_rows_serial(in_rows + y0, out_rows + y0, y1 - y0, W); });
+  }
+  for (auto& th : pool) th.join();
 }
 
 }  // namespace gol
