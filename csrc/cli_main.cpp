@@ -135,11 +135,30 @@ int main(int argc, char** argv) {
   gol_world_plan(w, &plan);
   if (json) {
     const double updates = (double)ranks * (double)cfg.rows * (double)cfg.width * (double)iters;
+    // per-phase device counters, summed over the local ranks (exposed halo wait = time edge warps
+    // spent spinning on a neighbour's flag)
+    gol_phase_counters_t pc, sum;
+    memset(&sum, 0, sizeof sum);
+    for (int r = 0; r < ranks; ++r) {
+      if (cpu || gol_world_phase_counters(w, r, &pc, 0)) break;
+      for (int i = 0; i < 2; ++i) {
+        sum.halo_wait_ns[i] += pc.halo_wait_ns[i];
+        sum.halo_waits[i] += pc.halo_waits[i];
+        sum.task_ns[i] += pc.task_ns[i];
+        sum.tasks[i] += pc.tasks[i];
+      }
+      sum.dep_wait_ns += pc.dep_wait_ns;
+    }
     printf("{\"gcups\": %.3f, \"seconds\": %.6f, \"mode\": %d, \"k\": %d, \"depth\": %d, "
-           "\"threads\": %d, \"strip_rows\": %d, \"launches\": %llu}\n",
+           "\"threads\": %d, \"strip_rows\": %d, \"launches\": %llu, "
+           "\"halo_wait_us\": [%.1f, %.1f], \"halo_waits\": [%llu, %llu], \"dep_wait_us\": %.1f, "
+           "\"task_us\": [%.1f, %.1f], \"tasks\": [%llu, %llu]}\n",
            seconds > 0 ? updates / seconds * 1e-9 : 0.0, seconds, plan.mode, plan.temporal_k,
            plan.exchange_depth, plan.threads_per_block, plan.strip_rows,
-           (unsigned long long)gol_launch_count());
+           (unsigned long long)gol_launch_count(), sum.halo_wait_ns[0] * 1e-3, sum.halo_wait_ns[1] * 1e-3,
+           (unsigned long long)sum.halo_waits[0], (unsigned long long)sum.halo_waits[1], sum.dep_wait_ns * 1e-3,
+           sum.task_ns[0] * 1e-3, sum.task_ns[1] * 1e-3, (unsigned long long)sum.tasks[0],
+           (unsigned long long)sum.tasks[1]);
   }
 
   int status = 0;

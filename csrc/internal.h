@@ -54,8 +54,15 @@ struct SlabState {
   unsigned long long exch;       // exchanges consumed -> recv parity
   unsigned long long words_seen; // flag value after the last consumed exchange
   unsigned int done;             // CTAs finished in the running launch
-  int error;                     // != 0: device-side failure (watchdog)
+  int error;                     // != 0: device-side failure (1 / 2: halo from prev / next timed out,
+                                 // 3: a strip dependency inside the flow kernel timed out)
   unsigned long long watchdog_ns;
+  // per-phase counters (tracing; accumulated by the kernels, read by gol_world_phase_counters)
+  unsigned long long wait_ns[2];   // time edge warps spent spinning on the [top, bottom] halo flag
+  unsigned long long wait_count[2];// ... and how many waits actually had to spin
+  unsigned long long dep_wait_ns;  // flow kernel: time warps spent waiting for a neighbouring strip
+  unsigned long long task_ns[2];   // flow kernel: [edge, interior] task time, summed over warps
+  unsigned long long tasks[2];     // flow kernel: [edge, interior] tasks executed
 };
 
 // Baked per launch (identical on every rank: the schedule is SPMD).
@@ -103,5 +110,58 @@ GOL_HD void strip_range(int order, int nstrips, int64_t first, int64_t end, int 
     if (*y1 > end) *y1 = end;
   }
 }
+
+// ---- strip decomposition of the flow (dependency-driven persistent) kernel ------------------
+// Strips are anchored to the slab's interior rows so that they are the same in every pass, whatever
+// the halo depth of the pass: strip 0 = top edge [-ext_out, E), strip n-1 = bottom edge
+// [H-E, H+ext_out), the n-2 interior strips split [E, H-E) evenly.  Task (pass p, strip j) reads
+// rows that strips j-1, j, j+1 wrote in pass p-1 and overwrites rows those strips read in pass p-1,
+// so it waits for exactly those three (when every strip has at least K rows).
+GOL_HD int flow_strip_count(int64_t H, int E, int strip_rows) {
+  if (H <= 2 * (int64_t)E) return 1;
+  const int64_t RI = H - 2 * (int64_t)E;
+  const int64_t n = (RI + strip_rows - 1) / strip_rows;
+  return 2 + (int)(n < 1 ? 1 : n);
+}
+GOL_HD void flow_strip_range(int j, int nstrips, int64_t H, int E, int ext_out, int64_t* y0, int64_t* y1) {
+  if (nstrips == 1) {
+    *y0 = -(int64_t)ext_out;
+    *y1 = H + ext_out;
+  } else if (j == 0) {
+    *y0 = -(int64_t)ext_out;
+    *y1 = E;
+  } else if (j == nstrips - 1) {
+    *y0 = H - E;
+    *y1 = H + ext_out;
+  } else {
+    const int64_t RI = H - 2 * (int64_t)E;
+    const int nint = nstrips - 2;
+    *y0 = E + (RI * (j - 1)) / nint;
+    *y1 = E + (RI * j) / nint;
+  }
+}
+// Ticket order inside a pass: both edge strips first (their halo push leaves early), then the
+// interior from the outside in, so that what a strip waits for was issued early in the pass before.
+GOL_HD int flow_order_to_strip(int q, int nstrips) {
+  if (q == 0) return 0;
+  if (q == 1) return nstrips - 1;
+  const int i = q - 2;
+  return (i & 1) ? nstrips - 2 - (i >> 1) : 1 + (i >> 1);
+}
+
+// Baked per launch of the flow kernel: `npasses` passes of K generations, halo exchange of `depth`
+// rows every passes_per_exchange passes (SPMD: identical on every rank).
+struct FlowParams {
+  int32_t npasses, passes_per_exchange, depth, nslabs;
+  int32_t col_groups, nstrips, edge_rows;
+  int32_t dep_radius;     // strips on each side a task waits for (1; nstrips when strips are shorter than K)
+  int32_t max_strips;     // pitch of `progress` per slab
+  int32_t total_warps;    // warps of the launch (the last one to finish resets the bookkeeping)
+  int32_t flags;          // experiments (GOL_FLOW_FLAGS): 1 = skip dependency waits (wrong results, timing
+                          // only), 4 = fixed owners (warp w always runs task slot w) instead of tickets,
+                          // 8 = no acquire fence after a dependency poll
+  unsigned int* ctl;      // [0] next ticket, [1] warps finished, [2] abort
+  unsigned int* progress; // [nslabs][max_strips] column-group tasks completed per strip in this launch
+};
 
 }  // namespace gol

@@ -28,19 +28,24 @@ constexpr unsigned kFull = 0xffffffffu;
 constexpr int kValidLanes = 30;  // lanes 1..30 own output columns
 
 // ---- system-scope ordering primitives --------------------------------------
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ void red_release_sys_add(unsigned long long* p, unsigned long long v) {
   asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+// Polling loads are relaxed; one acquire fence follows the successful poll.  (An acquire load or
+// fence at gpu / sys scope carries an L1 invalidate - SASS CCTL.IVALL - and polling with it slowed
+// every other warp of the SM by up to 50 %: measured with the flow kernel, 16384^2, B200.)
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned int ld_relaxed_gpu_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -54,21 +59,33 @@ __device__ __forceinline__ uint64_t ld_cg(const uint64_t* p) {
 
 // One lane spins until the neighbour has delivered `target` words (monotonic
 // counter).  A dead peer must not hang the GPU: after watchdog_ns the slab is
-// marked failed and the pass continues on whatever is in the buffer.
+// marked failed and the pass continues on whatever is in the buffer.  Time spent
+// spinning is accumulated per side (the "exposed halo wait" phase counter).
+// Called by ALL lanes of the warp (they poll the same word: one request per warp).  A wait run
+// by lane 0 alone, followed by __syncwarp(), leaves the warp split as far as the hardware's
+// convergence tracking goes, and every later __shfl_sync of the task then takes the slow
+// WARPSYNC.COLLECTIVE path (ncu: +57 % instructions executed, task time x2).
 __device__ __noinline__ void wait_words(SlabState* st, int side, unsigned long long target) {
   const unsigned long long* f = st->flag[side];
-  if (ld_acquire_sys(f) >= target) return;
-  const unsigned long long t0 = globaltimer_ns();
-  const unsigned long long limit = st->watchdog_ns;
-  unsigned ns = 0;   // poll back to back first: the data is usually a few hundred ns away
-  while (ld_acquire_sys(f) < target) {
-    if (ns) __nanosleep(ns);
-    ns = ns < 8 ? ns + 1 : (ns < 640 ? ns << 1 : ns);
-    if (globaltimer_ns() - t0 > limit) {
-      atomicExch(&st->error, 1 + side);
-      return;
+  const bool lane0 = (threadIdx.x & 31) == 0;
+  if (ld_relaxed_sys(f) < target) {
+    const unsigned long long t0 = globaltimer_ns();
+    const unsigned long long limit = st->watchdog_ns;
+    unsigned ns = 0;   // poll back to back first: the data is usually a few hundred ns away
+    while (ld_relaxed_sys(f) < target) {
+      if (ns) __nanosleep(ns);
+      ns = ns < 8 ? ns + 1 : (ns < 640 ? ns << 1 : ns);
+      if (globaltimer_ns() - t0 > limit || *(volatile int*)&st->error) {
+        if (lane0) atomicCAS(&st->error, 0, 1 + side);
+        break;
+      }
+    }
+    if (lane0) {
+      atomicAdd(&st->wait_ns[side], globaltimer_ns() - t0);
+      atomicAdd(&st->wait_count[side], 1ull);
     }
   }
+  fence_acq_rel_sys();   // relaxed load + fence = acquire: the halo rows are visible from here on
 }
 
 // Everything a pass needs about one slab, resolved from SlabState counters.
@@ -264,6 +281,76 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
   }
 }
 
+// Interior strips (no recv rows, no halo push): the same K-stage pipeline with the per-row address
+// arithmetic reduced to two pointer increments and the stores predicated instead of branched
+// around, so that the row loop is straight-line code: 88 LOP3/SHF + 8 SHFL + 1 LDG + 1 STG + 2 adds
+// per row at K = 4.  Nothing is read beyond row y1 + K - 1: caller-owned buffers (the no-allocation
+// entry point) have no rows to spare.
+template <int K, int V>
+__device__ __forceinline__ void stream_interior(const PassCtx& c, const TaskGeom& g) {
+  constexpr int B = 4;  // rows per batch (software prefetch depth)
+  const int64_t stride = c.stride;
+  const uint64_t* in = c.in + g.wi + (g.y0 - K) * stride;
+  uint64_t* out = c.out + g.wi + g.y0 * stride;
+  const bool owner = g.owner;
+  const int n_out = (int)(g.y1 - g.y0);
+
+  Stage s[K];
+#pragma unroll
+  for (int t = 0; t < K; ++t) {
+    s[t].lo.a0 = s[t].lo.a1 = s[t].lo.b0 = s[t].lo.b1 = s[t].lo.c = 0;
+    s[t].hi.a0 = s[t].hi.a1 = s[t].hi.b0 = s[t].hi.b1 = s[t].hi.c = 0;
+  }
+  // pipeline fill: the first 2K rows produce no output; row i only feeds stages 0..i/2
+  {
+    uint64_t pre[2 * K];
+#pragma unroll
+    for (int i = 0; i < 2 * K; ++i) {
+      pre[i] = ld_cg(in);
+      in += stride;
+    }
+#pragma unroll
+    for (int i = 0; i < 2 * K; ++i) push_row<K, V>(s, pre[i], (i / 2 + 1 < K) ? i / 2 + 1 : K);
+  }
+  // steady state: every row in yields one row out; whole batches first
+  const int nfull = n_out / B, rem = n_out - nfull * B;
+  uint64_t nxt[B];
+  if (nfull > 0) {
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      nxt[j] = ld_cg(in);
+      in += stride;
+    }
+  }
+#pragma unroll 1
+  for (int b = 0; b < nfull; ++b) {
+    uint64_t cur[B];
+#pragma unroll
+    for (int j = 0; j < B; ++j) cur[j] = nxt[j];
+    if (b + 1 < nfull) {
+#pragma unroll
+      for (int j = 0; j < B; ++j) {
+        nxt[j] = ld_cg(in);
+        in += stride;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const uint64_t o = push_row<K, V>(s, cur[j], K);
+      if (owner) st_cg(out, o);
+      out += stride;
+    }
+  }
+#pragma unroll 1
+  for (int j = 0; j < rem; ++j) {
+    const uint64_t x = ld_cg(in);
+    in += stride;
+    const uint64_t o = push_row<K, V>(s, x, K);
+    if (owner) st_cg(out, o);
+    out += stride;
+  }
+}
+
 // One warp task of a fused pass: strip `strip` of column group `cg`.
 __device__ __forceinline__ TaskGeom make_geom(const PassCtx& c, int64_t y0, int64_t y1, int cg, int lane) {
   TaskGeom g;
@@ -318,18 +405,16 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int6
   const bool reads_bot = c.consume && (g.y1 + K > c.H);
   int rows_top, rows_bot;
   push_ranges(c, g.y0, g.y1, &rows_top, &rows_bot);
-  if (reads_top || reads_bot) {
-    if (lane == 0) {
-      if (reads_top) wait_words(st, 0, c.target);
-      if (reads_bot) wait_words(st, 1, c.target);
-    }
+  if (reads_top || reads_bot) {   // warp-uniform: every lane polls (see wait_words)
+    if (reads_top) wait_words(st, 0, c.target);
+    if (reads_bot) wait_words(st, 1, c.target);
     __syncwarp();
   }
   if (reads_top || reads_bot || rows_top || rows_bot) {
     stream_rows<K, V, true>(c, g);    // recv-row sources and inline halo push
     publish_edges(st, c, g, lane);
   } else {
-    stream_rows<K, V, false>(c, g);
+    stream_interior<K, V>(c, g);
   }
 }
 
@@ -644,113 +729,148 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
   }
 }
 
-// ---- N-K3: persistent kernel ----------------------------------------------------
-// The whole generation loop of the reference (gol-main.c:94-116) in one
-// cooperative launch: prime, then npasses fused passes separated by a grid
-// barrier.  Halo flags from the ring neighbours are the only cross-GPU
-// synchronisation; the host is not involved until the end.
-__device__ __forceinline__ void grid_barrier(unsigned int* bar, unsigned int nctas,
-                                             unsigned int& epoch) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    ++epoch;
-    __threadfence();
-    atomicAdd(bar, 1u);
-    const unsigned int want = epoch * nctas;
-    while (ld_acquire_gpu_u32(bar) < want) {
+// ---- N-K3: persistent "flow" kernel ---------------------------------------------------
+// The whole generation loop of the reference (gol-main.c:94-116) in ONE ordinary launch, with no
+// grid-wide barrier between passes.  Every (pass, strip, column group) is a ticket; warps pull
+// tickets from a device counter in an order that is a topological order of the dependency graph
+// (pass-major, inside a pass the two edge strips first and then the interior from the outside
+// in).  A task of pass p waits - lane 0 with ld.acquire.gpu on per-strip progress counters - only
+// for the three strips of pass p-1 whose rows it reads and overwrites; it publishes its own
+// completion with red.release.gpu.  Passes therefore overlap: while the slow tail of pass p
+// finishes, free warps are already deep in pass p+1, and the SMs never drain between passes (the
+// per-pass launches of life_fused_kernel leave them empty for ~15 % of every 36 us pass).
+// Cross-GPU ordering is unchanged: edge tasks wait for the ring neighbours' halo words
+// (wait_words) and push their own edge rows as they produce them.
+//
+// Deadlock freedom: a warp waits only for tickets lower than its own, and a ticket is only ever
+// held by a running warp, so the launch needs neither co-residency of all CTAs nor a cooperative
+// launch.  Every wait is bounded by the slab's watchdog.
+__device__ __forceinline__ void red_release_gpu_add_u32(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Called by all lanes of the warp (see wait_words).
+__device__ __noinline__ void wait_strips(SlabState* st, unsigned int* ctl, const unsigned int* prog, int lo,
+                                         int hi, unsigned int want, int fence) {
+  const bool lane0 = (threadIdx.x & 31) == 0;
+  unsigned long long t0 = 0;
+  for (int jj = lo; jj <= hi; ++jj) {
+    if (ld_relaxed_gpu_u32(prog + jj) >= want) continue;
+    if (!t0) t0 = globaltimer_ns();
+    unsigned ns = 0;
+    while (ld_relaxed_gpu_u32(prog + jj) < want) {
+      if (ns) __nanosleep(ns);
+      ns = ns < 8 ? ns + 1 : (ns < 256 ? ns << 1 : ns);
+      if (globaltimer_ns() - t0 > st->watchdog_ns || *(volatile unsigned int*)&ctl[2]) {
+        if (lane0) {
+          atomicCAS(&st->error, 0, 3);
+          atomicExch(&ctl[2], 1u);
+        }
+        jj = hi;  // give up on the remaining strips too
+        break;
+      }
     }
   }
-  __syncthreads();
+  if (fence) fence_acq_rel_gpu();
+  if (t0 && lane0) atomicAdd(&st->dep_wait_ns, globaltimer_ns() - t0);
+}
+
+template <int K>
+__device__ __forceinline__ void flow_task(SlabState* states, const FlowParams& fp, int pass, unsigned slot,
+                                          unsigned percg, int lane) {
+  const int q = (int)(slot / percg);
+  const unsigned rem = slot - (unsigned)q * percg;
+  const int sidx = (int)(rem / (unsigned)fp.col_groups);
+  const int cg = (int)(rem - (unsigned)sidx * (unsigned)fp.col_groups);
+  const int j = flow_order_to_strip(q, fp.nstrips);
+  SlabState* st = states + sidx;
+
+  const int pos = pass % fp.passes_per_exchange;
+  const int ext_in = fp.depth - pos * K;
+  const int ext_out = ext_in - K;
+  const int consume = pos == 0;
+  const int push = (ext_out == 0 && pass + 1 < fp.npasses) ? fp.depth : 0;
+  const unsigned long long nex = (unsigned long long)(pass / fp.passes_per_exchange);
+  const unsigned long long exch = st->exch + nex + (consume ? 0ull : 1ull);
+  const unsigned long long seen = st->words_seen + nex * (unsigned long long)fp.depth * (unsigned long long)st->ws;
+  const PassCtx c = make_ctx(st, st->pass + (unsigned long long)pass, exch, seen, ext_in, consume, push);
+  int64_t y0, y1;
+  flow_strip_range(j, fp.nstrips, c.H, fp.edge_rows, ext_out, &y0, &y1);
+
+  unsigned int* prog = fp.progress + (size_t)sidx * (size_t)fp.max_strips;
+  if (pass > 0 && !(fp.flags & 1)) {
+    const int lo = j - fp.dep_radius, hi = j + fp.dep_radius;
+    wait_strips(st, fp.ctl, prog, lo < 0 ? 0 : lo, hi > fp.nstrips - 1 ? fp.nstrips - 1 : hi,
+                (unsigned)pass * (unsigned)fp.col_groups, !(fp.flags & 8));
+    __syncwarp();
+  }
+  const unsigned long long t0 = globaltimer_ns();
+  fused_task<K, 0>(st, c, y0, y1, cg, lane);
+  // every lane's stores happen-before lane 0's release through the warp barrier
+  __syncwarp();
+  if (lane == 0) {
+    red_release_gpu_add_u32(prog + j, 1u);
+    const int edge = (j == 0 || j == fp.nstrips - 1) ? 0 : 1;
+    atomicAdd(&st->task_ns[edge], globaltimer_ns() - t0);
+    atomicAdd(&st->tasks[edge], 1ull);
+  }
 }
 
 template <int K, int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB) life_persistent_kernel(SlabState* states,
-                                                                     PersistentParams pp) {
+__global__ void __launch_bounds__(MAXT, MINB) life_flow_kernel(SlabState* states, FlowParams fp) {
   const int lane = threadIdx.x & 31;
-  const int wpb = blockDim.x >> 5;
-  const int gwarp = blockIdx.x * wpb + (threadIdx.x >> 5);
-  const int nwarps = gridDim.x * wpb;
-  unsigned int epoch = 0;
+  const unsigned percg = (unsigned)(fp.nslabs * fp.col_groups);
+  const unsigned tpp = percg * (unsigned)fp.nstrips;          // tasks per pass
 
-  // counters at entry (identical for every slab of the launch by construction,
-  // but read per slab to stay general)
-  // prime: push `depth` edge rows of the current generation
-  {
-    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
-    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
-      SlabState* st = states + sidx;
-      const int64_t ws = st->ws, stride = st->stride, H = st->H;
-      const uint64_t* in = st->buf[st->pass & 1] + (int64_t)st->G * stride;
-      uint64_t* ptop = st->peer_recv[0][st->exch & 1];
-      uint64_t* pbot = st->peer_recv[1][st->exch & 1];
-      const int64_t per_side = (int64_t)pp.depth * ws;
-      int sent_top = 0, sent_bot = 0;
-      for (int64_t i = gtid; i < 2 * per_side; i += gthreads) {
-        const int side = i >= per_side;
-        const int64_t j = side ? i - per_side : i;
-        const int64_t r = j / ws, w = j - r * ws;
-        if (!side) {
-          st_cg(ptop + r * stride + w, in[r * stride + w]);
-          ++sent_top;
-        } else {
-          st_cg(pbot + r * stride + w, in[(H - pp.depth + r) * stride + w]);
-          ++sent_bot;
-        }
-      }
-      // publish once per CTA: block barrier, then one cumulative release by thread 0
-      __shared__ unsigned long long acc[2];
-      if (threadIdx.x == 0) acc[0] = acc[1] = 0;
-      __syncthreads();
-      if (sent_top) atomicAdd(&acc[0], (unsigned long long)sent_top);
-      if (sent_bot) atomicAdd(&acc[1], (unsigned long long)sent_bot);
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        if (acc[0]) red_release_sys_add(st->peer_flag[0], acc[0]);
-        if (acc[1]) red_release_sys_add(st->peer_flag[1], acc[1]);
-      }
-      __syncthreads();
+  if (!(fp.flags & 4)) {
+    // ticket mode (default): any free warp takes the next task in topological order
+    const unsigned total = tpp * (unsigned)fp.npasses;        // < 2^31 (bounded by the host)
+    for (;;) {
+      unsigned t = 0;
+      if (lane == 0) t = atomicAdd(&fp.ctl[0], 1u);
+      t = __shfl_sync(kFull, t, 0);
+      if (t >= total) break;
+      if (*(volatile unsigned int*)&fp.ctl[2]) continue;      // aborted: drain the tickets
+      const int pass = (int)(t / tpp);
+      flow_task<K>(states, fp, pass, t - (unsigned)pass * tpp, percg, lane);
+    }
+  } else {
+    // owner mode (GOL_FLOW_FLAGS=4): warp w runs the same task slot(s) w, w + nwarps, ... in every pass, so in steady
+    // state it only ever waits for the warps that own the neighbouring strips
+    const unsigned gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    for (int pass = 0; pass < fp.npasses; ++pass) {
+      if (*(volatile unsigned int*)&fp.ctl[2]) break;
+      for (unsigned slot = gw; slot < tpp; slot += (unsigned)fp.total_warps)
+        flow_task<K>(states, fp, pass, slot, percg, lane);
     }
   }
 
-  for (int pass = 0; pass < pp.npasses; ++pass) {
-    const int pos = pass % pp.passes_per_exchange;
-    const int ext_in = pp.depth - pos * K;
-    const int ext_out = ext_in - K;
-    const int consume = pos == 0;
-    const int push = (ext_out == 0 && pass + 1 < pp.npasses) ? pp.depth : 0;
-    const int nex = pass / pp.passes_per_exchange;  // exchanges fully consumed before this period
-    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
-      SlabState* st = states + sidx;
-      const unsigned long long pass0 = st->pass, exch0 = st->exch, seen0 = st->words_seen;
-      const unsigned long long exch = exch0 + (unsigned long long)nex + (consume ? 0ull : 1ull);
-      const unsigned long long seen =
-          seen0 + (unsigned long long)nex * (unsigned long long)pp.depth * (unsigned long long)st->ws;
-      const PassCtx c = make_ctx(st, pass0 + pass, exch, seen, ext_in, consume, push);
-      const int64_t rows_total = c.H + 2 * ext_out;
-      const int nstrips = strip_count(rows_total, pp.pass.strip_rows, pp.pass.edge_rows);
-      const int ntasks = nstrips * pp.pass.col_groups;
-      for (int task = gwarp; task < ntasks; task += nwarps) {
-        const int order = task / pp.pass.col_groups;
-        const int cg = task - order * pp.pass.col_groups;
-        int64_t y0, y1;
-        strip_range(order, nstrips, -(int64_t)ext_out, c.H + ext_out, pp.pass.strip_rows, pp.pass.edge_rows,
-                    &y0, &y1);
-        fused_task<K, 0>(st, c, y0, y1, cg, lane);
-      }
-    }
-    grid_barrier(pp.barrier, gridDim.x, epoch);
-  }
-
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    const int nex = (pp.npasses + pp.passes_per_exchange - 1) / pp.passes_per_exchange;
-    for (int sidx = 0; sidx < pp.nslabs; ++sidx) {
-      SlabState* st = states + sidx;
-      st->pass += (unsigned long long)pp.npasses;
-      st->exch += (unsigned long long)nex;
-      st->words_seen += (unsigned long long)nex * (unsigned long long)pp.depth * (unsigned long long)st->ws;
-    }
+  // the last warp out advances the slab counters and leaves the bookkeeping zeroed for the next launch
+  unsigned last = 0;
+  if (lane == 0) {
     __threadfence();
+    last = atomicAdd(&fp.ctl[1], 1u) == (unsigned)fp.total_warps - 1u;
+  }
+  last = __shfl_sync(kFull, last, 0);
+  if (last) {
+    __threadfence();
+    const unsigned long long nex =
+        (unsigned long long)((fp.npasses + fp.passes_per_exchange - 1) / fp.passes_per_exchange);
+    for (int sidx = lane; sidx < fp.nslabs; sidx += 32) {
+      SlabState* st = states + sidx;
+      st->pass += (unsigned long long)fp.npasses;
+      st->exch += nex;
+      st->words_seen += nex * (unsigned long long)fp.depth * (unsigned long long)st->ws;
+    }
+    const int n = fp.nslabs * fp.max_strips;
+    for (int i = lane; i < n; i += 32) fp.progress[i] = 0u;
+    __syncwarp();
+    if (lane == 0) {
+      fp.ctl[0] = 0u;
+      fp.ctl[1] = 0u;
+      fp.ctl[2] = 0u;
+      __threadfence();
+    }
   }
 }
 
@@ -955,11 +1075,24 @@ template <> struct FusedCfg<4> { static constexpr int kMaxT = 256, kMinB = 2; };
 template <> struct FusedCfg<6> { static constexpr int kMaxT = 128, kMinB = 3; };
 template <> struct FusedCfg<8> { static constexpr int kMaxT = 128, kMinB = 3; };
 
+// Occupancy experiment (GOL_EXP_MINB=3|4, K = 2 and 3 only): the same kernel compiled for more resident blocks.
+static int exp_minb() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GOL_EXP_MINB");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
 template <int K, int V = 0> const void* fused_fn() {
+  if (K == 2 || K == 3) {
+    if (exp_minb() == 3) return (const void*)&life_fused_kernel<(K == 2 || K == 3) ? K : 2, 256, 3, V>;
+    if (exp_minb() == 4) return (const void*)&life_fused_kernel<(K == 2 || K == 3) ? K : 2, 256, 4, V>;
+  }
   return (const void*)&life_fused_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB, V>;
 }
-template <int K> const void* persistent_fn() {
-  return (const void*)&life_persistent_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
+template <int K> const void* flow_fn() {
+  return (const void*)&life_flow_kernel<K, FusedCfg<K>::kMaxT, FusedCfg<K>::kMinB>;
 }
 
 #define GOL_DISPATCH_K(K, expr)                       \
@@ -1012,9 +1145,9 @@ int fused_resident_warps_per_sm(int K, int threads, int device) {
   return nb * (threads / 32);
 }
 
-int persistent_max_ctas(int K, int threads, int device) {
+int flow_max_ctas(int K, int threads, int device) {
   const void* fn = nullptr;
-  GOL_DISPATCH_K(K, fn = persistent_fn<KK>());
+  GOL_DISPATCH_K(K, fn = flow_fn<KK>());
   if (!fn) return 0;
   int nb = 0, sms = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, threads, 0) != cudaSuccess) {
@@ -1116,15 +1249,16 @@ cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max
   return cudaGetLastError();
 }
 
-cudaError_t launch_persistent(int K, SlabState* d_states, const PersistentParams& pp, int threads,
-                              int nctas, cudaStream_t s) {
+cudaError_t launch_flow(int K, SlabState* d_states, const FlowParams& fp0, int threads, int nctas,
+                        cudaStream_t s) {
   const void* fn = nullptr;
-  GOL_DISPATCH_K(K, fn = persistent_fn<KK>());
+  GOL_DISPATCH_K(K, fn = flow_fn<KK>());
   if (!fn) return cudaErrorInvalidValue;
-  PersistentParams p = pp;
-  void* args[] = {(void*)&d_states, (void*)&p};
+  FlowParams fp = fp0;
+  fp.total_warps = nctas * (threads / 32);
+  void* args[] = {(void*)&d_states, (void*)&fp};
   count_launch(1);
-  return cudaLaunchCooperativeKernel(fn, dim3((unsigned)nctas), dim3((unsigned)threads), args, 0, s);
+  return cudaLaunchKernel(fn, dim3((unsigned)nctas), dim3((unsigned)threads), args, 0, s);
 }
 
 static int grid_for(int64_t total, int threads) {

@@ -11,7 +11,8 @@ namespace gol {
 // Kernel inventory ("new-framework kernel list"):
 //   life_fused<K>      N-K1  register-streaming K-generation pass + P2P halo push + flags
 //   life_generic       N-K2  one thread per word, any shape, 1 generation, same protocol
-//   life_persistent<K> N-K3  whole step() in one cooperative launch (grid barrier between passes)
+//   life_flow<K>       N-K3  whole step() in one launch: persistent warps pull (pass, strip) tickets and
+//                            wait on per-strip progress counters instead of a grid barrier
 //   pattern_init       N-K4  patterns 0..6 straight into packed words
 //   halo_prime         N-K5  push my edge rows into the neighbours' recv buffers
 //   format_rows        N-K6  bits -> "0 1 0 ..." text rows on the device
@@ -26,7 +27,7 @@ bool fused_k_supported(int K);
 
 // Resident warps per SM for the fused kernel at a block size (occupancy query).
 int fused_resident_warps_per_sm(int K, int threads, int device);
-int persistent_max_ctas(int K, int threads, int device);
+int flow_max_ctas(int K, int threads, int device);
 
 cudaError_t launch_fused(int K, SlabState* d_states, int nslabs, const PassParams& p, int threads,
                          cudaStream_t s);
@@ -44,18 +45,11 @@ cudaError_t launch_generic(SlabState* d_states, int nslabs, const PassParams& p,
                            int64_t max_words, cudaStream_t s);
 cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max_ws, cudaStream_t s);
 
-// Persistent: `npasses` identical passes (K gens each, exchange every
-// `passes_per_exchange` passes of depth K * passes_per_exchange).
-struct PersistentParams {
-  PassParams pass;           // strip_rows / col_groups / nstrips for ext_out = 0 are recomputed on device
-  int32_t npasses;
-  int32_t passes_per_exchange;
-  int32_t depth;             // exchange depth = K * passes_per_exchange
-  int32_t nslabs;
-  unsigned int* barrier;     // 2 x u32 in device memory, zero before first use
-};
-cudaError_t launch_persistent(int K, SlabState* d_states, const PersistentParams& pp, int threads,
-                              int nctas, cudaStream_t s);
+// Flow (persistent) kernel: `npasses` passes of K generations in one launch, dependency-driven
+// (FlowParams in internal.h).  `nctas` CTAs of `threads` threads; ctl / progress must be zero before
+// the first launch (the kernel leaves them zeroed).
+cudaError_t launch_flow(int K, SlabState* d_states, const FlowParams& fp, int threads, int nctas,
+                        cudaStream_t s);
 
 cudaError_t launch_pattern_init(uint64_t* d_rows, int64_t stride, const PatternArgs& a,
                                 cudaStream_t s);

@@ -9,6 +9,7 @@
 // (R = 1, 2, >= 3) is testable without a GPU.
 #include <cuda_runtime.h>
 #include <errno.h>
+#include <stddef.h>
 #include <nvtx3/nvToolsExt.h>  // header-only; ranges show up in Nsight when a tool is attached
 #include <stdlib.h>
 #include <string.h>
@@ -83,7 +84,8 @@ struct Group {
   bool own_stream = false;
   std::vector<int> slabs;
   SlabState* d_states = nullptr;
-  unsigned int* d_barrier = nullptr;
+  unsigned int* d_barrier = nullptr;   // flow kernel control words: [0] ticket, [1] warps finished, [2] abort
+  unsigned int* d_progress = nullptr;  // flow kernel: [slabs][flow_strips] tasks completed per strip
   CUtensorMap* d_tmaps = nullptr;  // [slabs][2], TMA mode only
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   std::map<int64_t, std::pair<cudaGraphExec_t, int>> graphs;  // gens -> (exec, kernels)
@@ -113,7 +115,8 @@ struct gol_world {
   std::vector<Group> groups;
   std::vector<Peer> peers;
   uint64_t pass_host = 0;  // passes enqueued so far (buffer parity of every slab)
-  int resident_warps = 0, sms = 148;
+  int resident_warps = 0, sms = 0;
+  int flow_strips = 0;     // strips per slab of the flow kernel (fixed for the world)
 };
 
 namespace gol {
@@ -239,7 +242,7 @@ int finish_plan_cuda(gol_world* w) {
   int slots = w->sms * rw / std::max(1, slabs_per_dev);
   if (p.mode == GOL_MODE_PERSISTENT) {
     const int wpb = p.threads_per_block / 32;
-    const int ctas = persistent_max_ctas(p.temporal_k, p.threads_per_block, dev);
+    const int ctas = flow_max_ctas(p.temporal_k, p.threads_per_block, dev);
     if (ctas > 0) slots = ctas * wpb / std::max(1, slabs_per_dev);
   }
   // the two edge strips (exchange_depth rows each) are tasks of their own; the interior is tuned
@@ -248,11 +251,30 @@ int finish_plan_cuda(gol_world* w) {
   const int tw = fused_tma_warps(p.col_groups);
   const int cg_eff = p.mode == GOL_MODE_TMA ? (p.col_groups + tw - 1) / tw * tw : p.col_groups;
   p.strip_rows = pick_strip_rows(interior, cg_eff, p.temporal_k, slots, w->sms);
+  if (p.mode == GOL_MODE_PERSISTENT) {
+    // The flow kernel hands tickets to free warps: it wants about three tasks per resident warp and
+    // pass so that a free warp always finds one whose neighbours are done, but not strips so short
+    // that the 2K pipeline-fill rows dominate (measured on B200: 36 rows at 16384^2, 64 at
+    // 65536 x 8192, 128 at 131072 x 16384, 256 at 65536^2; profiles/flow_kernel.md).
+    const int64_t per_warp = interior * cg_eff / (3 * (int64_t)std::max(1, slots));
+    p.strip_rows = (int)std::max<int64_t>(std::max(9 * p.temporal_k, p.exchange_depth), (per_warp + 3) / 4 * 4);
+    if (p.strip_rows > interior) p.strip_rows = (int)interior;
+  }
   if (w->cfg.reserved > 0) p.strip_rows = w->cfg.reserved;   // explicit strip height (tuning / experiments)
   const int wpb = p.threads_per_block / 32;
   const int64_t strips = strip_count(w->H, p.strip_rows, p.exchange_depth);
   p.ctas_per_slab = (int)((strips * p.col_groups + wpb - 1) / wpb);
   p.regs_hint = rw;
+  if (p.mode == GOL_MODE_PERSISTENT) {
+    // bookkeeping of the flow kernel: one progress counter per strip and slab
+    w->flow_strips = flow_strip_count(w->H, p.exchange_depth, p.strip_rows);
+    for (auto& g : w->groups) {
+      CU_TRY(cudaSetDevice(g.device));
+      const size_t n = g.slabs.size() * (size_t)w->flow_strips * sizeof(unsigned int);
+      CU_TRY(cudaMalloc((void**)&g.d_progress, n));
+      CU_TRY(cudaMemset(g.d_progress, 0, n));
+    }
+  }
   return GOL_OK;
 }
 
@@ -689,6 +711,7 @@ void gol_world_destroy(gol_world_t* w) {
       if (g.e1) cudaEventDestroy(g.e1);
       if (g.d_states) cudaFree(g.d_states);
       if (g.d_barrier) cudaFree(g.d_barrier);
+      if (g.d_progress) cudaFree(g.d_progress);
       if (g.d_tmaps) cudaFree(g.d_tmaps);
       if (g.own_stream && g.stream) cudaStreamDestroy(g.stream);
     }
@@ -814,7 +837,25 @@ static int resolve_peer_base(gol_world* w, int rank, int for_device, char** base
   if (!p.imported) return set_error(GOL_ERR_STATE, "rank %d is neither local nor imported", rank);
   if (!p.mapped) {
     if (p.blob.pid == (int32_t)getpid()) {
-      p.mapped = (char*)(uintptr_t)p.blob.base_addr;  // another world in this process
+      // another world in this process: its pointer is usable as is on the same device, through
+      // peer access on a different one
+      if (p.blob.device != for_device) {
+        if (w->cfg.flags & GOL_FLAG_NO_PEER_ACCESS)
+          return set_error(GOL_ERR_CUDA, "rank %d lives on device %d and peer access is disabled", rank,
+                           p.blob.device);
+        int can = 0;
+        CU_TRY(cudaDeviceCanAccessPeer(&can, for_device, p.blob.device));
+        if (!can)
+          return set_error(GOL_ERR_CUDA, "device %d cannot access device %d (no P2P path)", for_device,
+                           p.blob.device);
+        CU_TRY(cudaSetDevice(for_device));
+        cudaError_t e = cudaDeviceEnablePeerAccess(p.blob.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+          return set_error(GOL_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d->%d): %s", for_device, p.blob.device,
+                           cudaGetErrorString(e));
+        cudaGetLastError();
+      }
+      p.mapped = (char*)(uintptr_t)p.blob.base_addr;
     } else {
       CU_TRY(cudaSetDevice(for_device));
       void* ptr = nullptr;
@@ -1050,32 +1091,46 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
     if (periods > 0 && !launch) {
       todo -= periods * pl.exchange_depth;
     } else if (periods > 0) {
-      const int64_t max_periods = (int64_t)(1 << 20);
+      // One launch of the flow kernel per chunk of exchange periods; tickets are 32-bit.
+      const int K = pl.temporal_k, E = pl.exchange_depth;
+      const int nstrips = w->flow_strips;
+      int dep_radius = 1;
+      if (nstrips > 2 && (w->H - 2 * (int64_t)E) / (nstrips - 2) < K) dep_radius = nstrips;
+      const int wpb = pl.threads_per_block / 32;
+      int64_t max_tpp = 1;
+      for (auto& g : w->groups)
+        max_tpp = std::max<int64_t>(max_tpp, (int64_t)g.slabs.size() * nstrips * pl.col_groups);
+      const int64_t max_periods = std::max<int64_t>(1, std::min<int64_t>(1 << 20, ((1ll << 31) - 1) / max_tpp / P));
       int64_t left = periods;
       while (left > 0) {
         const int64_t now = std::min(left, max_periods);
         for (auto& g : w->groups) {
           CU_TRY(cudaSetDevice(g.device));
-          PersistentParams pp;
-          memset(&pp, 0, sizeof pp);
-          pp.pass.ext_in = pl.exchange_depth;
-          pp.pass.k = pl.temporal_k;
-          pp.pass.strip_rows = pl.strip_rows;
-          pp.pass.edge_rows = pl.exchange_depth;
-          pp.pass.col_groups = pl.col_groups;
-          pp.npasses = (int)(now * P);
-          pp.passes_per_exchange = P;
-          pp.depth = pl.exchange_depth;
-          pp.nslabs = (int)g.slabs.size();
-          pp.barrier = g.d_barrier;
-          const int wpb = pl.threads_per_block / 32;
-          const int64_t rows_total = w->H + 2 * (pl.exchange_depth - pl.temporal_k);
-          const int64_t tasks = (int64_t)strip_count(rows_total, pl.strip_rows, pl.exchange_depth) * pl.col_groups;
-          int nctas = persistent_max_ctas(pl.temporal_k, pl.threads_per_block, g.device);
-          if (nctas < 1) return set_error(GOL_ERR_CUDA, "persistent kernel cannot be made resident");
-          nctas = (int)std::min<int64_t>(nctas, (tasks + wpb - 1) / wpb);
-          CU_TRY(cudaMemsetAsync(g.d_barrier, 0, 8, g.stream));
-          CU_TRY(launch_persistent(pl.temporal_k, g.d_states, pp, pl.threads_per_block, nctas, g.stream));
+          FlowParams fp;
+          memset(&fp, 0, sizeof fp);
+          fp.npasses = (int)(now * P);
+          fp.passes_per_exchange = P;
+          fp.depth = E;
+          fp.nslabs = (int)g.slabs.size();
+          fp.col_groups = pl.col_groups;
+          fp.nstrips = nstrips;
+          fp.edge_rows = E;
+          fp.dep_radius = dep_radius;
+          fp.max_strips = nstrips;
+          fp.ctl = g.d_barrier;
+          fp.progress = g.d_progress;
+          if (const char* e = getenv("GOL_FLOW_FLAGS")) fp.flags = atoi(e);
+          const int64_t tpp = (int64_t)fp.nslabs * nstrips * pl.col_groups;
+          int nctas = flow_max_ctas(K, pl.threads_per_block, g.device);
+          if (nctas < 1) return set_error(GOL_ERR_CUDA, "flow kernel does not fit an SM");
+          // owner mode: one warp per task slot; ticket mode: more warps than two passes' worth of
+          // tasks could only spin on dependencies
+          const int64_t want_warps = (fp.flags & 4) ? tpp : 2 * tpp;
+          nctas = (int)std::max<int64_t>(1, std::min<int64_t>(nctas, (want_warps + wpb - 1) / wpb));
+          if (const char* e = getenv("GOL_FLOW_CTAS"))
+            if (atoi(e) > 0) nctas = std::min(nctas, atoi(e));
+          CU_TRY(launch_prime(g.d_states, fp.nslabs, E, w->ws, g.stream));
+          CU_TRY(launch_flow(K, g.d_states, fp, pl.threads_per_block, nctas, g.stream));
         }
         w->pass_host += (uint64_t)(now * P);
         left -= now;
@@ -1206,6 +1261,33 @@ int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms) {
     CU_TRY(cudaSetDevice(g.device));
     CU_TRY(cudaEventElapsedTime(&t, g.e0, g.e1));
     for (int si : g.slabs) ms[si] = t;
+  }
+  return GOL_OK;
+}
+
+int gol_world_phase_counters(gol_world_t* w, int li, gol_phase_counters_t* out, int reset) {
+  int rc = check_local(w, li);
+  if (rc) return rc;
+  if (!out) return set_error(GOL_ERR_ARG, "null output");
+  memset(out, 0, sizeof *out);
+  if (!w->cuda) return GOL_OK;
+  Slab& s = w->slabs[(size_t)li];
+  Group& g = w->groups[(size_t)s.group];
+  CU_TRY(cudaSetDevice(s.device));
+  CU_TRY(cudaStreamSynchronize(g.stream));
+  SlabState* d = g.d_states + s.index_in_group;
+  SlabState h;
+  CU_TRY(cudaMemcpy(&h, d, sizeof h, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 2; ++i) {
+    out->halo_wait_ns[i] = h.wait_ns[i];
+    out->halo_waits[i] = h.wait_count[i];
+    out->task_ns[i] = h.task_ns[i];
+    out->tasks[i] = h.tasks[i];
+  }
+  out->dep_wait_ns = h.dep_wait_ns;
+  if (reset) {
+    const size_t off = offsetof(SlabState, wait_ns);
+    CU_TRY(cudaMemset((char*)d + off, 0, sizeof(SlabState) - off));
   }
   return GOL_OK;
 }

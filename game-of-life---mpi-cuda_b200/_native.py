@@ -60,6 +60,11 @@ class _Plan(C.Structure):
     ]
 
 
+class _PhaseCounters(C.Structure):
+    _fields_ = [("halo_wait_ns", C.c_uint64 * 2), ("halo_waits", C.c_uint64 * 2), ("dep_wait_ns", C.c_uint64),
+                ("task_ns", C.c_uint64 * 2), ("tasks", C.c_uint64 * 2)]
+
+
 def _load() -> C.CDLL:
     _build_if_missing()
     lib = C.CDLL(_LIB_PATH, mode=C.RTLD_GLOBAL)
@@ -96,6 +101,7 @@ def _load() -> C.CDLL:
         "gol_world_step": (I32, [VP, I64]),
         "gol_world_sync": (I32, [VP]),
         "gol_world_step_timed": (I32, [VP, I64, P(C.c_float)]),
+        "gol_world_phase_counters": (I32, [VP, I32, P(_PhaseCounters), I32]),
         "gol_world_device_ptr": (VP, [VP, I32]),
         "gol_world_device_of": (I32, [VP, I32]),
         "gol_world_cpu_get_edge": (I32, [VP, I32, I32, VP]),
@@ -289,6 +295,19 @@ class World:
         ms = (C.c_float * self.nlocal)()
         check(lib.gol_world_step_timed(self._h, int(gens), ms))
         return list(ms)
+
+    def phase_counters(self, local: int = 0, reset: bool = False) -> dict:
+        """Device-side per-phase counters (see ``gol_phase_counters_t``): exposed halo wait per side,
+        strip-dependency wait and edge / interior task time of the persistent kernel."""
+        pc = _PhaseCounters()
+        check(lib.gol_world_phase_counters(self._h, local, C.byref(pc), int(reset)))
+        return {
+            "halo_wait_ns": [int(pc.halo_wait_ns[0]), int(pc.halo_wait_ns[1])],
+            "halo_waits": [int(pc.halo_waits[0]), int(pc.halo_waits[1])],
+            "dep_wait_ns": int(pc.dep_wait_ns),
+            "task_ns": {"edge": int(pc.task_ns[0]), "interior": int(pc.task_ns[1])},
+            "tasks": {"edge": int(pc.tasks[0]), "interior": int(pc.tasks[1])},
+        }
 
     # -- views / io
     def device_ptr(self, local: int = 0) -> int:

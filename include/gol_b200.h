@@ -37,7 +37,8 @@ extern "C" {
 #define GOL_MODE_AUTO 0        /* fused where the shape allows, else generic   */
 #define GOL_MODE_GENERIC 1     /* one thread per word, any W/H, 1 gen per pass  */
 #define GOL_MODE_FUSED 2       /* register-streaming, K generations per pass    */
-#define GOL_MODE_PERSISTENT 3  /* one cooperative launch for the whole step()   */
+#define GOL_MODE_PERSISTENT 3  /* one launch for the whole step(): persistent warps,
+                                  per-strip dependencies instead of grid barriers */
 #define GOL_MODE_TMA 4         /* fused, input rows fed by TMA bulk copies      */
 
 #define GOL_MAX_GHOST 32       /* deepest exchange (rows per side)              */
@@ -159,6 +160,20 @@ int gol_world_step(gol_world_t* w, int64_t gens);
 int gol_world_sync(gol_world_t* w);
 /* Same, bracketed by CUDA events: ms[i] = device time of local slab i's stream. */
 int gol_world_step_timed(gol_world_t* w, int64_t gens, float* ms /* nlocal */);
+
+/* Per-phase counters accumulated on the device by the step kernels (tracing; the reference has
+ * one host wall-clock interval, gol-main.c:82,122).  halo_wait_ns[side]: time edge warps spent
+ * spinning on the [top, bottom] neighbour's halo flag, summed over the warps that had to wait
+ * (halo_waits[side] of them): the exposed halo time.  dep_wait_ns: time warps of the persistent
+ * kernel waited for a neighbouring strip of the previous pass.  task_ns / tasks: warp time and
+ * count of [edge, interior] strip tasks (persistent kernel).  Synchronises the slab's stream;
+ * reset != 0 zeroes the counters afterwards. */
+typedef struct gol_phase_counters {
+  uint64_t halo_wait_ns[2], halo_waits[2];
+  uint64_t dep_wait_ns;
+  uint64_t task_ns[2], tasks[2];
+} gol_phase_counters_t;
+int gol_world_phase_counters(gol_world_t* w, int local_index, gol_phase_counters_t* out, int reset);
 
 /* Device pointer of the current packed slab interior (row 0, word 0) for
  * zero-copy views; stride in words via gol_world_plan(). */

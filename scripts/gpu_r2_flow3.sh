@@ -1,0 +1,24 @@
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_property.py -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+tail -3 gpurun_out/pytest_gpu.log
+: > gpurun_out/flow3.log
+run() { echo "# $*" >> gpurun_out/flow3.log; timeout 120 env "$@" 2>&1 | tail -1 >> gpurun_out/flow3.log; }
+B="./bin/gol 6 16384 1024 256 0 --json --k 4 --mode persistent"
+run GOL_FLOW_FLAGS=0 $B
+run GOL_FLOW_FLAGS=8 $B
+run GOL_FLOW_FLAGS=1 $B
+run GOL_FLOW_FLAGS=4 $B
+run GOL_FLOW_FLAGS=12 $B
+run GOL_FLOW_FLAGS=4 $B --strip 56
+run GOL_FLOW_FLAGS=4 $B --strip 48
+run GOL_FLOW_FLAGS=4 $B --strip 31
+run GOL_FLOW_FLAGS=0 $B --strip 64
+run GOL_FLOW_FLAGS=0 $B --strip 66
+run GOL_FLOW_FLAGS=0 $B --strip 72
+run GOL_FLOW_FLAGS=0 $B --strip 31
+run GOL_FLOW_FLAGS=0 ./bin/gol 6 4096 4096 256 0 --json --k 4 --mode persistent
+run GOL_FLOW_FLAGS=0 ./bin/gol 6 4096 4096 256 0 --json --k 4 --mode persistent --strip 20
+run GOL_FLOW_FLAGS=4 ./bin/gol 6 4096 4096 256 0 --json --k 4 --mode persistent
+run GOL_FLOW_FLAGS=0 ./bin/gol 6 65536 16 256 0 --json --k 4 --mode persistent
+run GOL_FLOW_FLAGS=0 ./bin/gol 6 65536 64 256 0 --json --k 4 --rows 8192 --mode persistent
+cat gpurun_out/flow3.log
