@@ -4,6 +4,10 @@
 #   baseline/_ref/bin/gol_ref     the reference as shipped (official bar)
 #   baseline/_ref/bin/gol_ref_noprintf   steelman: the device printf at gol-with-cuda.cu:223
 #                                 removed in a build-time copy (the ONLY change)
+#   baseline/_ref/bin/gol_ref_rect[_noprintf]   strong-scaling variant: the reference's main with ONE change made
+#                                 at build time - gol_initMaster (gol-main.c:76) gets (W, H) =
+#                                 (worldSize, $GOL_REF_ROWS) instead of (worldSize, worldSize); the .cu is
+#                                 untouched (its API already takes W and H, gol-with-cuda.cu:286)
 #   baseline/_ref/bin/mpirun      minimpi launcher (this image has no MPI)
 # The reference ships no build file; flags follow SURVEY.md section 6.3.
 set -euo pipefail
@@ -28,4 +32,16 @@ if cmp -s "$OUT/src/gol-with-cuda.cu" "$OUT/obj/gol-with-cuda-noprintf.cu"; then
 fi
 nvcc -O3 $ARCH -w -c "$OUT/obj/gol-with-cuda-noprintf.cu" -o "$OUT/obj/gol-with-cuda-noprintf.o"
 nvcc $ARCH -o "$OUT/bin/gol_ref_noprintf" "$OUT/obj/gol-main.o" "$OUT/obj/gol-with-cuda-noprintf.o" "$OUT/obj/minimpi.o" -lrt
+# strong-scaling variant: rectangular slabs through the unchanged .cu API
+sed '76s/gol_initMaster(pattern, worldSize, worldSize, myRank, numRank);/gol_initMaster(pattern, worldSize, getenv("GOL_REF_ROWS") ? (unsigned int)atoi(getenv("GOL_REF_ROWS")) : worldSize, myRank, numRank);/' \
+  "$OUT/src/gol-main.c" > "$OUT/obj/gol-main-rect.c"
+if cmp -s "$OUT/src/gol-main.c" "$OUT/obj/gol-main-rect.c"; then
+  echo "build_ref: gol_initMaster call not found at gol-main.c:76" >&2; exit 1
+fi
+if [ "$(diff "$OUT/src/gol-main.c" "$OUT/obj/gol-main-rect.c" | grep -c '^[<>]')" != "2" ]; then
+  echo "build_ref: the rectangular variant differs from gol-main.c in more than one line" >&2; exit 1
+fi
+gcc -O2 -w -I"$HERE/minimpi" -c "$OUT/obj/gol-main-rect.c" -o "$OUT/obj/gol-main-rect.o"
+nvcc $ARCH -o "$OUT/bin/gol_ref_rect" "$OUT/obj/gol-main-rect.o" "$OUT/obj/gol-with-cuda.o" "$OUT/obj/minimpi.o" -lrt
+nvcc $ARCH -o "$OUT/bin/gol_ref_rect_noprintf" "$OUT/obj/gol-main-rect.o" "$OUT/obj/gol-with-cuda-noprintf.o" "$OUT/obj/minimpi.o" -lrt
 echo "built: $(ls "$OUT/bin")"

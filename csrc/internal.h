@@ -41,12 +41,24 @@ struct SlabState {
   int64_t ws;          // valid words per row
   int64_t stride;      // row stride in words
   int32_t G;           // margin rows per side (= GOL_MAX_GHOST capped by plan)
+  int32_t ll_ring;     // bit 0 / 1: halo rows from / to the prev / next neighbour use the LL form
   int32_t rank, nranks;
-  int32_t pad0;
+  int32_t local_ring;  // bit 0 / 1: the prev / next ring neighbour lives on THIS device, so its flag
+                       // and halo rows need gpu scope only.  System-scope fences travel to the host
+                       // bridge: while a PCIe copy is in flight each one waits behind it, and the
+                       // step kernels ran 25 % slower under a concurrent upload (B200, measured).
   // storage (all device pointers valid on the device that runs this slab)
   uint64_t* buf[2];              // buf[pass & 1] is the current generation
   uint64_t* recv[2][2];          // [side 0=top,1=bottom][exchange parity], G x stride each
   uint64_t* peer_recv[2][2];     // [0]: prev rank's bottom recv, [1]: next rank's top recv
+  // Halo rows from a neighbour on ANOTHER device travel in flag-in-data ("LL") form: every 64-bit
+  // halo word is sent as two 8-byte words {32 data bits | 32-bit exchange number}, each written
+  // by one atomic 8-byte store, and the reader polls the data itself until both halves carry the
+  // expected number.  No flag, no release / acquire fence on either side: a system-scope fence
+  // waits for the host bridge as well, which costs microseconds and, while a PCIe copy is in
+  // flight, far more (see local_ring).  Layout: word w of halo row r at ll[(r * stride + w) * 2].
+  uint64_t* ll_recv[2][2];       // [side][exchange parity], 2 * G * stride words each
+  uint64_t* peer_ll[2][2];       // [0]: prev rank's bottom ll_recv, [1]: next rank's top ll_recv
   unsigned long long* flag[2];       // words received so far on [top, bottom] (monotonic)
   unsigned long long* peer_flag[2];  // [0]: prev's bottom flag, [1]: next's top flag
   // counters advanced by the kernels

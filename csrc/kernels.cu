@@ -20,6 +20,10 @@
 
 #include "kernels.cuh"
 
+#ifndef GOL_FUSED_COHERENT
+#define GOL_FUSED_COHERENT 0   // 1: per-pass fused kernel also uses ld/st.global.cg for interior rows
+#endif
+
 namespace gol {
 
 namespace {
@@ -31,6 +35,51 @@ constexpr int kValidLanes = 30;  // lanes 1..30 own output columns
 __device__ __forceinline__ void red_release_sys_add(unsigned long long* p, unsigned long long v) {
   asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ void red_release_gpu_add(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Publish `v` more halo words to a ring neighbour: gpu scope when the neighbour's slab is on this
+// device, system scope (NVLink peer) otherwise.
+__device__ __forceinline__ void publish_words(const SlabState* st, int side, unsigned long long v) {
+  if ((st->local_ring >> side) & 1) red_release_gpu_add(st->peer_flag[side], v);
+  else red_release_sys_add(st->peer_flag[side], v);
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// ---- flag-in-data halo words (SlabState::ll_recv) ------------------------------------------------
+__device__ __forceinline__ void ll_store(uint64_t* p, uint64_t v, uint32_t seq) {
+  const unsigned long long a = (v & 0xffffffffull) | ((unsigned long long)seq << 32);
+  const unsigned long long b = (v >> 32) | ((unsigned long long)seq << 32);
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+// Warp-uniform: every lane polls its own word, the warp leaves together (a lane-divergent spin
+// would leave the warp split for the shuffles that follow).
+__device__ __noinline__ uint64_t ll_load(SlabState* st, const uint64_t* p, uint32_t seq, int side) {
+  unsigned long long a, b;
+  unsigned long long t0 = 0;
+  unsigned ns = 0;
+  for (;;) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    const bool ok = (uint32_t)(a >> 32) == seq && (uint32_t)(b >> 32) == seq;
+    if (__all_sync(0xffffffffu, ok)) break;
+    if (!t0) t0 = globaltimer_ns();
+    if (ns) __nanosleep(ns);
+    ns = ns < 8 ? ns + 1 : (ns < 640 ? ns << 1 : ns);
+    if (globaltimer_ns() - t0 > st->watchdog_ns || *(volatile int*)&st->error) {
+      if ((threadIdx.x & 31) == 0) atomicCAS(&st->error, 0, 1 + side);
+      break;
+    }
+  }
+  if (t0 && (threadIdx.x & 31) == 0) {
+    atomicAdd(&st->wait_ns[side], globaltimer_ns() - t0);
+    atomicAdd(&st->wait_count[side], 1ull);
+  }
+  return (a & 0xffffffffull) | (b << 32);
+}
+
 // Polling loads are relaxed; one acquire fence follows the successful poll.  (An acquire load or
 // fence at gpu / sys scope carries an L1 invalidate - SASS CCTL.IVALL - and polling with it slowed
 // every other warp of the SM by up to 50 %: measured with the flow kernel, 16384^2, B200.)
@@ -45,12 +94,12 @@ __device__ __forceinline__ unsigned int ld_relaxed_gpu_u32(const unsigned int* p
   return v;
 }
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
-__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
+__device__ __forceinline__ unsigned long long ld_relaxed_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
 }
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 // Peer / streaming stores: the output of a pass is not re-read by this SM.
 __device__ __forceinline__ void st_cg(uint64_t* p, uint64_t v) { __stcg((unsigned long long*)p, v); }
 __device__ __forceinline__ uint64_t ld_cg(const uint64_t* p) {
@@ -68,11 +117,12 @@ __device__ __forceinline__ uint64_t ld_cg(const uint64_t* p) {
 __device__ __noinline__ void wait_words(SlabState* st, int side, unsigned long long target) {
   const unsigned long long* f = st->flag[side];
   const bool lane0 = (threadIdx.x & 31) == 0;
-  if (ld_relaxed_sys(f) < target) {
+  const bool local = (st->local_ring >> side) & 1;   // the writer is on this device: gpu scope
+  if ((local ? ld_relaxed_gpu(f) : ld_relaxed_sys(f)) < target) {
     const unsigned long long t0 = globaltimer_ns();
     const unsigned long long limit = st->watchdog_ns;
     unsigned ns = 0;   // poll back to back first: the data is usually a few hundred ns away
-    while (ld_relaxed_sys(f) < target) {
+    while ((local ? ld_relaxed_gpu(f) : ld_relaxed_sys(f)) < target) {
       if (ns) __nanosleep(ns);
       ns = ns < 8 ? ns + 1 : (ns < 640 ? ns << 1 : ns);
       if (globaltimer_ns() - t0 > limit || *(volatile int*)&st->error) {
@@ -85,7 +135,9 @@ __device__ __noinline__ void wait_words(SlabState* st, int side, unsigned long l
       atomicAdd(&st->wait_count[side], 1ull);
     }
   }
-  fence_acq_rel_sys();   // relaxed load + fence = acquire: the halo rows are visible from here on
+  // relaxed load + fence = acquire: the halo rows are visible from here on
+  if (local) fence_acq_rel_gpu();
+  else fence_acq_rel_sys();
 }
 
 // Everything a pass needs about one slab, resolved from SlabState counters.
@@ -99,9 +151,17 @@ struct PassCtx {
   unsigned long long target;
   int64_t H, ws, stride;
   int ext_in, consume, push;
+  // flag-in-data halo path (neighbours on other devices)
+  SlabState* st;
+  const uint64_t* lltop;  // my top ll_recv of this exchange: halo row y (< 0) word w at ((y + ext_in) * stride + w) * 2
+  const uint64_t* llbot;  // my bottom ll_recv: row y (>= H) at ((y - H) * stride + w) * 2
+  uint64_t* pll_top;      // prev rank's bottom ll_recv for the exchange being pushed
+  uint64_t* pll_bot;      // next rank's top ll_recv
+  uint32_t seq_in, seq_out;
+  int ll;                 // SlabState::ll_ring
 };
 
-__device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long long pass,
+__device__ __forceinline__ PassCtx make_ctx(SlabState* st, unsigned long long pass,
                                             unsigned long long exch, unsigned long long words_seen,
                                             int ext_in, int consume, int push) {
   PassCtx c;
@@ -120,6 +180,14 @@ __device__ __forceinline__ PassCtx make_ctx(const SlabState* st, unsigned long l
   c.ext_in = ext_in;
   c.consume = consume;
   c.push = push;
+  c.st = st;
+  c.ll = st->ll_ring;
+  c.lltop = st->ll_recv[0][exch & 1];
+  c.llbot = st->ll_recv[1][exch & 1];
+  c.pll_top = st->peer_ll[0][pe & 1];
+  c.pll_bot = st->peer_ll[1][pe & 1];
+  c.seq_in = (uint32_t)(exch + 1ull);    // exchange numbers start at 1: zeroed memory never matches
+  c.seq_out = (uint32_t)(pe + 1ull);
   return c;
 }
 
@@ -229,6 +297,9 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
     const int64_t y = y_in + i;
     const uint64_t* p = in_col + y * c.stride;
     if (EDGE && fresh) {
+      // y is warp-uniform, so these branches are too
+      if (y < 0 && (c.ll & 1)) return ll_load(c.st, c.lltop + ((y + c.ext_in) * c.stride + g.wi) * 2, c.seq_in, 0);
+      if (y >= c.H && (c.ll & 2)) return ll_load(c.st, c.llbot + ((y - c.H) * c.stride + g.wi) * 2, c.seq_in, 1);
       p = (y < 0) ? top_col + y * c.stride : p;
       p = (y >= c.H) ? bot_col + y * c.stride : p;
     }
@@ -273,8 +344,14 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
       if (g.owner && y < g.y1) {
         st_cg(out_col + y * c.stride, o);
         if (EDGE && c.push) {
-          if (y >= 0 && y < push_lo) st_cg(ptop_col + y * c.stride, o);
-          if (y >= push_hi && y < c.H) st_cg(pbot_col + y * c.stride, o);
+          if (y >= 0 && y < push_lo) {
+            if (c.ll & 1) ll_store(c.pll_top + (y * c.stride + g.wi) * 2, o, c.seq_out);
+            else st_cg(ptop_col + y * c.stride, o);
+          }
+          if (y >= push_hi && y < c.H) {
+            if (c.ll & 2) ll_store(c.pll_bot + ((y - push_hi) * c.stride + g.wi) * 2, o, c.seq_out);
+            else st_cg(pbot_col + y * c.stride, o);
+          }
         }
       }
     }
@@ -286,7 +363,21 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
 // around, so that the row loop is straight-line code: 88 LOP3/SHF + 8 SHFL + 1 LDG + 1 STG + 2 adds
 // per row at K = 4.  Nothing is read beyond row y1 + K - 1: caller-owned buffers (the no-allocation
 // entry point) have no rows to spare.
-template <int K, int V>
+// COH = true (flow kernel): rows written by other SMs earlier in the SAME launch are read, so loads
+// and stores go to L2 (ld/st.global.cg).  COH = false (one launch per pass): the input is
+// read-only for the whole launch and L1 is invalidated at every launch boundary, so plain
+// accesses are enough.
+template <bool COH>
+__device__ __forceinline__ uint64_t ld_row(const uint64_t* p) {
+  return COH ? ld_cg(p) : *p;
+}
+template <bool COH>
+__device__ __forceinline__ void st_row(uint64_t* p, uint64_t v) {
+  if (COH) st_cg(p, v);
+  else *p = v;
+}
+
+template <int K, int V, bool COH>
 __device__ __forceinline__ void stream_interior(const PassCtx& c, const TaskGeom& g) {
   constexpr int B = 4;  // rows per batch (software prefetch depth)
   const int64_t stride = c.stride;
@@ -306,7 +397,7 @@ __device__ __forceinline__ void stream_interior(const PassCtx& c, const TaskGeom
     uint64_t pre[2 * K];
 #pragma unroll
     for (int i = 0; i < 2 * K; ++i) {
-      pre[i] = ld_cg(in);
+      pre[i] = ld_row<COH>(in);
       in += stride;
     }
 #pragma unroll
@@ -318,7 +409,7 @@ __device__ __forceinline__ void stream_interior(const PassCtx& c, const TaskGeom
   if (nfull > 0) {
 #pragma unroll
     for (int j = 0; j < B; ++j) {
-      nxt[j] = ld_cg(in);
+      nxt[j] = ld_row<COH>(in);
       in += stride;
     }
   }
@@ -330,23 +421,23 @@ __device__ __forceinline__ void stream_interior(const PassCtx& c, const TaskGeom
     if (b + 1 < nfull) {
 #pragma unroll
       for (int j = 0; j < B; ++j) {
-        nxt[j] = ld_cg(in);
+        nxt[j] = ld_row<COH>(in);
         in += stride;
       }
     }
 #pragma unroll
     for (int j = 0; j < B; ++j) {
       const uint64_t o = push_row<K, V>(s, cur[j], K);
-      if (owner) st_cg(out, o);
+      if (owner) st_row<COH>(out, o);
       out += stride;
     }
   }
 #pragma unroll 1
   for (int j = 0; j < rem; ++j) {
-    const uint64_t x = ld_cg(in);
+    const uint64_t x = ld_row<COH>(in);
     in += stride;
     const uint64_t o = push_row<K, V>(s, x, K);
-    if (owner) st_cg(out, o);
+    if (owner) st_row<COH>(out, o);
     out += stride;
   }
 }
@@ -382,6 +473,8 @@ __device__ __forceinline__ void push_ranges(const PassCtx& c, int64_t y0, int64_
 __device__ __forceinline__ void publish_edges(SlabState* st, const PassCtx& c, const TaskGeom& g, int lane) {
   int rows_top, rows_bot;
   push_ranges(c, g.y0, g.y1, &rows_top, &rows_bot);
+  if (c.ll & 1) rows_top = 0;   // flag-in-data sides need no publication
+  if (c.ll & 2) rows_bot = 0;
   if (rows_top | rows_bot) {
     // No per-lane fence: the warp barrier orders every lane's stores before lane 0's
     // red.release.sys, and a release is cumulative over what happens-before it.  (A per-lane
@@ -390,14 +483,14 @@ __device__ __forceinline__ void publish_edges(SlabState* st, const PassCtx& c, c
     __syncwarp();
     const unsigned owners = __popc(__ballot_sync(kFull, g.owner));
     if (lane == 0) {
-      if (rows_top) red_release_sys_add(st->peer_flag[0], (unsigned long long)owners * rows_top);
-      if (rows_bot) red_release_sys_add(st->peer_flag[1], (unsigned long long)owners * rows_bot);
+      if (rows_top) publish_words(st, 0, (unsigned long long)owners * rows_top);
+      if (rows_bot) publish_words(st, 1, (unsigned long long)owners * rows_bot);
     }
   }
 }
 
 // One warp task of a fused pass: output rows [y0, y1) of column group `cg`.
-template <int K, int V>
+template <int K, int V, bool COH = true>
 __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int64_t y0, int64_t y1,
                                            int cg, int lane) {
   const TaskGeom g = make_geom(c, y0, y1, cg, lane);
@@ -405,16 +498,16 @@ __device__ __forceinline__ void fused_task(SlabState* st, const PassCtx& c, int6
   const bool reads_bot = c.consume && (g.y1 + K > c.H);
   int rows_top, rows_bot;
   push_ranges(c, g.y0, g.y1, &rows_top, &rows_bot);
-  if (reads_top || reads_bot) {   // warp-uniform: every lane polls (see wait_words)
-    if (reads_top) wait_words(st, 0, c.target);
-    if (reads_bot) wait_words(st, 1, c.target);
+  if ((reads_top && !(c.ll & 1)) || (reads_bot && !(c.ll & 2))) {   // warp-uniform: every lane polls (see wait_words)
+    if (reads_top && !(c.ll & 1)) wait_words(st, 0, c.target);
+    if (reads_bot && !(c.ll & 2)) wait_words(st, 1, c.target);
     __syncwarp();
   }
   if (reads_top || reads_bot || rows_top || rows_bot) {
     stream_rows<K, V, true>(c, g);    // recv-row sources and inline halo push
     publish_edges(st, c, g, lane);
   } else {
-    stream_interior<K, V>(c, g);
+    stream_interior<K, V, COH>(c, g);
   }
 }
 
@@ -458,7 +551,7 @@ __global__ void __launch_bounds__(MAXT, MINB) life_fused_kernel(SlabState* state
     const int ext_out = p.ext_in - K;
     int64_t y0, y1;
     strip_range(order, p.nstrips, -(int64_t)ext_out, c.H + ext_out, p.strip_rows, p.edge_rows, &y0, &y1);
-    fused_task<K, V>(st, c, y0, y1, cg, lane);
+    fused_task<K, V, GOL_FUSED_COHERENT != 0>(st, c, y0, y1, cg, lane);
   }
   finish_pass(st, p, gridDim.x);
 }
@@ -686,8 +779,8 @@ __global__ void life_generic_kernel(SlabState* states, PassParams p) {
     const int nt = __syncthreads_count(sent_top);   // block barrier + cumulative release below
     const int nb = __syncthreads_count(sent_bot);
     if (threadIdx.x == 0) {
-      if (nt) red_release_sys_add(st->peer_flag[0], (unsigned long long)nt);
-      if (nb) red_release_sys_add(st->peer_flag[1], (unsigned long long)nb);
+      if (nt) publish_words(st, 0, (unsigned long long)nt);
+      if (nb) publish_words(st, 1, (unsigned long long)nb);
     }
   }
   finish_pass(st, p, gridDim.x);
@@ -702,6 +795,10 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
   const uint64_t* in = st->buf[st->pass & 1] + (int64_t)st->G * stride;
   uint64_t* ptop = st->peer_recv[0][st->exch & 1];
   uint64_t* pbot = st->peer_recv[1][st->exch & 1];
+  uint64_t* lltop = st->peer_ll[0][st->exch & 1];
+  uint64_t* llbot = st->peer_ll[1][st->exch & 1];
+  const uint32_t seq = (uint32_t)(st->exch + 1ull);
+  const int ll = st->ll_ring;
   const int64_t per_side = (int64_t)depth * ws;
   int sent_top = 0, sent_bot = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * per_side;
@@ -710,11 +807,21 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
     const int64_t j = side ? i - per_side : i;
     const int64_t r = j / ws, w = j - r * ws;
     if (!side) {
-      st_cg(ptop + r * stride + w, in[r * stride + w]);
-      ++sent_top;
+      const uint64_t v = in[r * stride + w];
+      if (ll & 1) {
+        ll_store(lltop + (r * stride + w) * 2, v, seq);   // flag-in-data: nothing to publish
+      } else {
+        st_cg(ptop + r * stride + w, v);
+        ++sent_top;
+      }
     } else {
-      st_cg(pbot + r * stride + w, in[(H - depth + r) * stride + w]);
-      ++sent_bot;
+      const uint64_t v = in[(H - depth + r) * stride + w];
+      if (ll & 2) {
+        ll_store(llbot + (r * stride + w) * 2, v, seq);
+      } else {
+        st_cg(pbot + r * stride + w, v);
+        ++sent_bot;
+      }
     }
   }
   __shared__ unsigned long long acc[2];
@@ -724,8 +831,8 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
   if (sent_bot) atomicAdd(&acc[1], (unsigned long long)sent_bot);
   __syncthreads();
   if (threadIdx.x == 0) {
-    if (acc[0]) red_release_sys_add(st->peer_flag[0], acc[0]);
-    if (acc[1]) red_release_sys_add(st->peer_flag[1], acc[1]);
+    if (acc[0]) publish_words(st, 0, acc[0]);
+    if (acc[1]) publish_words(st, 1, acc[1]);
   }
 }
 

@@ -101,6 +101,7 @@ extern "C" int gol_cuda_run_torus_noalloc(uint64_t* d_a, uint64_t* d_b, int64_t 
   st.G = 0;  // caller buffers have no margin rows: every pass takes its halo from recv[]
   st.rank = 0;
   st.nranks = 1;
+  st.local_ring = 3;  // a one-rank ring: both neighbours are this slab itself
   st.buf[0] = d_a;
   st.buf[1] = d_b;
   st.flag[0] = reinterpret_cast<unsigned long long*>(scratch + 512);

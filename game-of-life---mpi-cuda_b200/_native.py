@@ -98,6 +98,9 @@ def _load() -> C.CDLL:
         "gol_world_population": (I32, [VP, I32, P(U64)]),
         "gol_world_load_packed_async": (I32, [VP, I32, VP]),
         "gol_world_population_async": (I32, [VP, I32, VP]),
+        "gol_world_read_packed_async": (I32, [VP, I32, VP]),
+        "gol_world_run_from_host_async": (I32, [VP, P(VP), I64, P(VP)]),
+        "gol_world_wait_result": (I32, [VP, I32]),
         "gol_world_step": (I32, [VP, I64]),
         "gol_world_sync": (I32, [VP]),
         "gol_world_step_timed": (I32, [VP, I64, P(C.c_float)]),
@@ -267,9 +270,60 @@ class World:
         check(lib.gol_world_read_bytes(self._h, local, out.ctypes.data))
         return out
 
+    def _check_packed(self, words, what: str) -> None:
+        """A packed slab is rows x stride 64-bit words, contiguous, in HOST memory."""
+        if isinstance(words, int):
+            return                      # raw address: the caller vouches for it
+        n = self.rows * self.stride
+        if isinstance(words, np.ndarray):
+            if words.dtype.itemsize != 8 or words.size != n or not words.flags["C_CONTIGUOUS"]:
+                raise ValueError(f"{what}: expected a contiguous array of {self.rows}x{self.stride} 64-bit words, "
+                                 f"got shape {words.shape} dtype {words.dtype}")
+            return
+        if hasattr(words, "data_ptr"):  # torch tensor
+            if words.is_cuda:
+                raise ValueError(f"{what}: expected host memory, got a CUDA tensor")
+            if words.element_size() != 8 or words.numel() != n or not words.is_contiguous():
+                raise ValueError(f"{what}: expected a contiguous tensor of {self.rows}x{self.stride} 64-bit words, "
+                                 f"got shape {tuple(words.shape)} dtype {words.dtype}")
+            return
+        raise TypeError(f"{what}: cannot take the address of {type(words)!r}")
+
     def load_packed(self, local: int, words, asynchronous: bool = False) -> None:
+        """Upload a packed slab (rows x stride uint64, interleaved layout).  Bits beyond column
+        ``width`` in the last word of a row must be zero (the kernels rely on it); numpy inputs are
+        checked, other inputs are the caller's responsibility."""
+        self._check_packed(words, "load_packed")
+        if isinstance(words, np.ndarray) and self.width % 64:
+            last = words.reshape(self.rows, self.stride)[:, self.words - 1].view(np.uint64)
+            t = self.width % 64
+            mask = np.uint64(((1 << ((t + 1) >> 1)) - 1) | (((1 << (t >> 1)) - 1) << 32))
+            if np.any(last & ~mask):
+                raise ValueError("load_packed: bits set beyond the last column of a row")
         fn = lib.gol_world_load_packed_async if asynchronous else lib.gol_world_load_packed
         check(fn(self._h, local, _ptr(words)))
+
+    def read_packed_async(self, local: int, pinned_out) -> None:
+        """Queue a device-to-host copy of the current packed slab into pinned host memory."""
+        self._check_packed(pinned_out, "read_packed_async")
+        check(lib.gol_world_read_packed_async(self._h, local, _ptr(pinned_out)))
+
+    def run_from_host_async(self, pinned_in: Sequence, gens: int, pinned_out: Sequence) -> int:
+        """One pipelined end-to-end step (see ``gol_world_run_from_host_async``): returns the slot to
+        pass to :meth:`wait_result`."""
+        if len(pinned_in) != self.nlocal or len(pinned_out) != self.nlocal:
+            raise ValueError(f"expected {self.nlocal} input and output buffers")
+        for b in list(pinned_in) + list(pinned_out):
+            self._check_packed(b, "run_from_host_async")
+        ins = (C.c_void_p * self.nlocal)(*[_ptr(b) for b in pinned_in])
+        outs = (C.c_void_p * self.nlocal)(*[_ptr(b) for b in pinned_out])
+        slot = lib.gol_world_run_from_host_async(self._h, ins, int(gens), outs)
+        if slot < 0:
+            raise GolError(f"[{slot}] {last_error()}")
+        return int(slot)
+
+    def wait_result(self, slot: int) -> None:
+        check(lib.gol_world_wait_result(self._h, int(slot)))
 
     def read_packed(self, local: int = 0) -> np.ndarray:
         out = np.empty((self.rows, self.stride), dtype=np.uint64)

@@ -127,14 +127,23 @@ class Life:
             ms = float(t.item())
         return ms
 
-    def run_from_host(self, pinned_words, generations: int, pinned_result, local: int = 0) -> None:
-        """End-to-end step as a user would issue it: upload a packed world from pinned host
-        memory, advance it, and queue the population read-back into ``pinned_result`` (one
-        uint64 of pinned host memory).  Asynchronous; call :meth:`sync` before reading."""
-        self.world.load_packed(local, pinned_words, asynchronous=True)
-        self.world.step(generations)
-        self.world.population_async(local, pinned_result)
+    def run_from_host(self, pinned_words, generations: int, pinned_result) -> int:
+        """End-to-end step as a user issues it: upload a packed world from pinned host memory,
+        advance it, bring the packed result grid back into pinned host memory.  ``pinned_words`` /
+        ``pinned_result`` are one buffer (``rows x stride`` 64-bit words) or a list with one buffer
+        per local slab.  Asynchronous and pipelined: uploads, compute and downloads of consecutive
+        calls overlap (two slots).  Returns the slot for :meth:`wait_result`."""
+        ins = list(pinned_words) if isinstance(pinned_words, (list, tuple)) else [pinned_words]
+        outs = list(pinned_result) if isinstance(pinned_result, (list, tuple)) else [pinned_result]
+        slot = self.world.run_from_host_async(ins, generations, outs)
         self.generation += generations
+        return slot
+
+    def wait_result(self, slot: int) -> "Life":
+        """Block until the result of the :meth:`run_from_host` call that returned ``slot`` is in
+        host memory."""
+        self.world.wait_result(slot)
+        return self
 
     # ---------------------------------------------------------------- metrics
     def population(self, global_sum: bool = True) -> int:

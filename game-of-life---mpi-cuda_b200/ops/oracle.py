@@ -17,6 +17,18 @@ def oracle_run(cells: np.ndarray, generations: int) -> np.ndarray:
     return _native.oracle_run(cells, generations)
 
 
+def numpy_life_run(cells: np.ndarray, generations: int) -> np.ndarray:
+    """True torus Life with numpy ``roll`` on a 0/1 byte grid.  Shares nothing with the native
+    code (no ``life_math.h``, no packing): the independent check for wide grids, where the
+    byte-per-cell C oracle is slow and the packed CPU stepper shares its math with the kernels."""
+    g = np.ascontiguousarray(cells, dtype=np.uint8)
+    for _ in range(int(generations)):
+        v = g + np.roll(g, 1, axis=0) + np.roll(g, -1, axis=0)         # vertical 3-sums (<= 3)
+        n = v + np.roll(v, 1, axis=1) + np.roll(v, -1, axis=1) - g     # 8 neighbours (<= 8)
+        g = ((n == 3) | ((g == 1) & (n == 2))).astype(np.uint8)
+    return g
+
+
 def _step_with_ghosts(slab: np.ndarray, top: np.ndarray, bottom: np.ndarray) -> np.ndarray:
     ext = np.vstack([top[None, :], slab, bottom[None, :]]).astype(np.int32)
     n = np.zeros_like(ext)

@@ -50,6 +50,17 @@ class ClockSampler:
         self._thread.start()
         return self
 
+    def wait_first_sample(self, timeout_s: float = 10.0) -> bool:
+        """nvidia-smi needs a second or more before its first line arrives (longer with eight ranks
+        starting at once): block until it has, so that a short timed region is not left without a
+        clock record."""
+        t_end = time.time() + timeout_s
+        while not self.samples and time.time() < t_end:
+            if self._proc is None or self._proc.poll() is not None:
+                return False
+            time.sleep(0.05)
+        return bool(self.samples)
+
     def stop(self, t0: Optional[float] = None, t1: Optional[float] = None) -> Dict:
         if self._proc is not None:
             self._proc.terminate()

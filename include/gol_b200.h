@@ -153,6 +153,20 @@ int gol_world_population(gol_world_t* w, int local_index, uint64_t* count);     
 int gol_world_load_packed_async(gol_world_t* w, int local_index, const uint64_t* pinned_words);
 int gol_world_population_async(gol_world_t* w, int local_index, uint64_t* pinned_out);
 
+int gol_world_read_packed_async(gol_world_t* w, int local_index, uint64_t* pinned_words);
+
+/* End-to-end step pipeline.  One call uploads this step's packed input of every local slab from
+ * pinned host memory (pinned_in[i], H * stride words), advances `gens` generations and brings
+ * the packed result back into pinned_out[i].  Upload and download use their own copy streams and
+ * two slots of device staging, so consecutive calls overlap: the input of step i+1 travels while
+ * step i computes, and the result of step i travels while step i+1 computes.  Returns the slot
+ * (0 or 1) to hand to gol_world_wait_result(), which blocks until that step's result is in host
+ * memory; at most two steps may be outstanding.  Negative = error.  (The reference reaches its
+ * data through managed memory and has no explicit copies, gol-with-cuda.cu:35-67.) */
+int gol_world_run_from_host_async(gol_world_t* w, const uint64_t* const* pinned_in, int64_t gens,
+                                  uint64_t* const* pinned_out);
+int gol_world_wait_result(gol_world_t* w, int slot);
+
 /* Advance every local slab by `gens` generations (halo exchange fused in).
  * Asynchronous on CUDA; gol_world_sync waits and reports device-side errors
  * (flag-wait watchdog, bad launch). */

@@ -286,3 +286,19 @@ def test_slab_larger_than_2_pow_31_cells():
     pop = w.population(0)
     assert abs(pop / float(W * H) - 0.5) < 1e-3
     w.close()
+
+
+# ------------------------------------------------------------------ flag-in-data halo rows
+@pytest.mark.parametrize("mode,k,depth,R", [("fused", 4, 4, 1), ("fused", 4, 4, 2), ("fused", 4, 4, 3),
+                                            ("fused", 2, 8, 2), ("fused", 8, 32, 3), ("fused", 1, 1, 2),
+                                            ("persistent", 4, 4, 2), ("persistent", 2, 4, 3), ("tma", 4, 4, 2)])
+def test_flag_in_data_halo_protocol(monkeypatch, mode, k, depth, R):
+    """Halo rows between devices travel as {32 data bits | exchange number} words with no flag and no
+    fence.  GOL_FORCE_LL=1 routes same-device neighbours through that path too, so one GPU covers
+    it; the rings of two and three ranks exercise both parities of the receive slots."""
+    monkeypatch.setenv("GOL_FORCE_LL", "1")
+    W, H = (10240, 96) if mode == "tma" else (2048, 80)
+    gens = 5 * depth + 3
+    got, plan = run_gpu(6, W, H, R, gens, mode=mode, k=k, depth=depth, seed=41, chunks=[depth + 1, gens - depth - 1])
+    assert plan["mode_name"] == mode
+    assert (got == expected(6, W, H, R, gens, seed=41)).all()

@@ -105,3 +105,19 @@ def test_reference_quirk_model_matches_survey_table():
     assert first_divergence(4, 2, 64) == 1         # swapped ghosts at R <= 2
     assert first_divergence(4, 3, 64) == 2         # stale halos from generation 2 on
     assert first_divergence(1, 4, 64) == 2
+
+
+@pytest.mark.parametrize("w,h,gens", [(1000, 20, 5), (2048, 24, 7), (4096, 17, 6), (4100, 9, 4), (1920, 33, 9)])
+def test_packed_stepper_at_multi_kiloword_widths_vs_numpy(w, h, gens):
+    """The packed CPU stepper is what most GPU tests compare with, and it shares life_math.h with the
+    kernels: pin it to the independent numpy stepper at the widths where column groups, tail
+    masks and the x seam matter (it was only pinned for widths <= 200)."""
+    from gol_b200.ops.oracle import numpy_life_run
+
+    rng = np.random.default_rng(w + h)
+    g = (rng.random((h, w)) < 0.5).astype(np.uint8)
+    want = numpy_life_run(g, gens)
+    assert (numpy_life(g, gens) == want).all()
+    assert (n.unpack(n.cpu_run_packed(n.pack(g), w, gens), w) == want).all()
+    if w <= 2048:
+        assert (oracle_run(g, gens) == want).all()
