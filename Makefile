@@ -14,7 +14,25 @@ CU_SRCS   := $(wildcard $(CU_SRCS))
 OBJS      := $(patsubst csrc/%.cu,$(OBJDIR)/%.o,$(CU_SRCS)) $(patsubst csrc/%.cpp,$(OBJDIR)/%.o,$(CXX_SRCS))
 HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
 
-all: $(LIB) $(BIN)
+DBGLIB    := $(PKG)/_lib/libgol_b200_debug.so
+DBGOBJS   := $(patsubst csrc/%.cu,$(OBJDIR)/debug/%.o,$(CU_SRCS)) $(patsubst csrc/%.cpp,$(OBJDIR)/debug/%.o,$(CXX_SRCS))
+
+all: $(LIB) $(BIN) $(DBGLIB)
+
+# bounds-checking build: same sources with -DGOL_DEBUG_BOUNDS=1 (include/gol_b200.h, "Memory-safety build")
+$(OBJDIR)/debug/%.o: csrc/%.cu $(HDRS)
+	@mkdir -p $(OBJDIR)/debug
+	$(NVCC) $(NVFLAGS) -DGOL_DEBUG_BOUNDS=1 -c $< -o $@
+
+$(OBJDIR)/debug/%.o: csrc/%.cpp $(HDRS)
+	@mkdir -p $(OBJDIR)/debug
+	$(NVCC) $(NVFLAGS) -DGOL_DEBUG_BOUNDS=1 -x cu -c $< -o $@
+
+$(DBGLIB): $(DBGOBJS)
+	@mkdir -p $(dir $@)
+	$(NVCC) $(ARCH) -shared -o $@ $(DBGOBJS) -lcudart_static -ldl -lrt -lpthread
+
+debug: $(DBGLIB)
 
 $(OBJDIR)/%.o: csrc/%.cu $(HDRS)
 	@mkdir -p $(OBJDIR)
@@ -43,6 +61,6 @@ test-gpu: all
 	python -m pytest tests -q -m gpu
 
 clean:
-	rm -rf $(OBJDIR) $(LIB) $(BIN)
+	rm -rf $(OBJDIR) $(LIB) $(DBGLIB) $(BIN)
 
-.PHONY: all clean sass test test-gpu
+.PHONY: all clean sass test test-gpu debug

@@ -24,18 +24,55 @@
 #define GOL_FUSED_COHERENT 0   // 1: per-pass fused kernel also uses ld/st.global.cg for interior rows
 #endif
 
+#ifndef GOL_DEBUG_BOUNDS
+#define GOL_DEBUG_BOUNDS 0     // 1: libgol_b200_debug.so - every global access of every kernel is checked
+#endif
+
 namespace gol {
 
 namespace {
+
+#if GOL_DEBUG_BOUNDS
+// Memory-safety build (compute-sanitizer is closed on the GPU pool this was developed on): the
+// host registers every allocation a kernel may touch - slab buffers, halo mailboxes (own and
+// mapped neighbours'), text / byte scratch, partial sums, caller buffers of the stateless calls -
+// and every global load, store and atomic of every kernel first looks its address range up.  A
+// miss is counted, its address and source line are kept, and the access is skipped.
+constexpr int kDbgMaxRegions = 96;
+struct DebugRegions {
+  unsigned long long lo[kDbgMaxRegions], hi[kDbgMaxRegions];
+  int n;
+  int first_line;
+  unsigned long long violations;
+  unsigned long long first_bad;
+};
+__device__ DebugRegions g_dbg;
+__device__ __noinline__ bool dbg_ok(const void* p, long long bytes, int line) {
+  const unsigned long long a = (unsigned long long)p, b = a + (unsigned long long)bytes;
+  const int n = g_dbg.n;
+  for (int i = 0; i < n; ++i)
+    if (a >= g_dbg.lo[i] && b <= g_dbg.hi[i]) return true;
+  if (atomicAdd(&g_dbg.violations, 1ull) == 0ull) {
+    g_dbg.first_bad = a;
+    g_dbg.first_line = line;
+  }
+  return false;
+}
+#define GOL_CHK(p, n) dbg_ok((const void*)(p), (long long)(n), __LINE__)
+#else
+#define GOL_CHK(p, n) (true)
+#endif
 
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kValidLanes = 30;  // lanes 1..30 own output columns
 
 // ---- system-scope ordering primitives --------------------------------------
 __device__ __forceinline__ void red_release_sys_add(unsigned long long* p, unsigned long long v) {
+  if (!GOL_CHK(p, 8)) return;
   asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void red_release_gpu_add(unsigned long long* p, unsigned long long v) {
+  if (!GOL_CHK(p, 8)) return;
   asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 // Publish `v` more halo words to a ring neighbour: gpu scope when the neighbour's slab is on this
@@ -51,6 +88,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 // ---- flag-in-data halo words (SlabState::ll_recv) ------------------------------------------------
 __device__ __forceinline__ void ll_store(uint64_t* p, uint64_t v, uint32_t seq) {
+  if (!GOL_CHK(p, 16)) return;
   const unsigned long long a = (v & 0xffffffffull) | ((unsigned long long)seq << 32);
   const unsigned long long b = (v >> 32) | ((unsigned long long)seq << 32);
   asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
@@ -61,6 +99,7 @@ __device__ __noinline__ uint64_t ll_load(SlabState* st, const uint64_t* p, uint3
   unsigned long long a, b;
   unsigned long long t0 = 0;
   unsigned ns = 0;
+  if (!GOL_CHK(p, 16)) return 0;
   for (;;) {
     asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
     const bool ok = (uint32_t)(a >> 32) == seq && (uint32_t)(b >> 32) == seq;
@@ -84,25 +123,32 @@ __device__ __noinline__ uint64_t ll_load(SlabState* st, const uint64_t* p, uint3
 // fence at gpu / sys scope carries an L1 invalidate - SASS CCTL.IVALL - and polling with it slowed
 // every other warp of the SM by up to 50 %: measured with the flow kernel, 16384^2, B200.)
 __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  if (!GOL_CHK(p, 8)) return ~0ull;
   unsigned long long v;
   asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ unsigned int ld_relaxed_gpu_u32(const unsigned int* p) {
+  if (!GOL_CHK(p, 4)) return ~0u;
   unsigned int v;
   asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ unsigned long long ld_relaxed_gpu(const unsigned long long* p) {
+  if (!GOL_CHK(p, 8)) return ~0ull;
   unsigned long long v;
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 // Peer / streaming stores: the output of a pass is not re-read by this SM.
-__device__ __forceinline__ void st_cg(uint64_t* p, uint64_t v) { __stcg((unsigned long long*)p, v); }
+__device__ __forceinline__ void st_cg(uint64_t* p, uint64_t v) {
+  if (!GOL_CHK(p, 8)) return;
+  __stcg((unsigned long long*)p, v);
+}
 __device__ __forceinline__ uint64_t ld_cg(const uint64_t* p) {
+  if (!GOL_CHK(p, 8)) return 0;
   return __ldcg((const unsigned long long*)p);
 }
 
@@ -369,12 +415,13 @@ __device__ __forceinline__ void stream_rows(const PassCtx& c, const TaskGeom& g)
 // accesses are enough.
 template <bool COH>
 __device__ __forceinline__ uint64_t ld_row(const uint64_t* p) {
+  if (!COH && !GOL_CHK(p, 8)) return 0;
   return COH ? ld_cg(p) : *p;
 }
 template <bool COH>
 __device__ __forceinline__ void st_row(uint64_t* p, uint64_t v) {
   if (COH) st_cg(p, v);
-  else *p = v;
+  else if (GOL_CHK(p, 8)) *p = v;
 }
 
 template <int K, int V, bool COH>
@@ -768,8 +815,10 @@ __global__ void life_generic_kernel(SlabState* states, PassParams p) {
     const uint64_t* cur = c.in + y * c.stride;
     const uint64_t* up = (y == 0 && p.consume) ? c.rtop : cur - c.stride;
     const uint64_t* down = (y == c.H - 1 && p.consume) ? c.rbot : cur + c.stride;
-    const uint64_t v = step_word(up, cur, down, w, c.ws, st->W);
-    c.out[y * c.stride + w] = v;
+    uint64_t v = 0;
+    if (GOL_CHK(up, c.ws * 8) && GOL_CHK(cur, c.ws * 8) && GOL_CHK(down, c.ws * 8))
+      v = step_word(up, cur, down, w, c.ws, st->W);
+    if (GOL_CHK(c.out + y * c.stride + w, 8)) c.out[y * c.stride + w] = v;
     if (p.push) {
       if (y == 0) { st_cg(c.ptop + w, v); sent_top = 1; }
       if (y == c.H - 1) { st_cg(c.pbot + w, v); sent_bot = 1; }
@@ -807,7 +856,7 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
     const int64_t j = side ? i - per_side : i;
     const int64_t r = j / ws, w = j - r * ws;
     if (!side) {
-      const uint64_t v = in[r * stride + w];
+      const uint64_t v = GOL_CHK(in + r * stride + w, 8) ? in[r * stride + w] : 0;
       if (ll & 1) {
         ll_store(lltop + (r * stride + w) * 2, v, seq);   // flag-in-data: nothing to publish
       } else {
@@ -815,7 +864,7 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
         ++sent_top;
       }
     } else {
-      const uint64_t v = in[(H - depth + r) * stride + w];
+      const uint64_t v = GOL_CHK(in + (H - depth + r) * stride + w, 8) ? in[(H - depth + r) * stride + w] : 0;
       if (ll & 2) {
         ll_store(llbot + (r * stride + w) * 2, v, seq);
       } else {
@@ -853,6 +902,7 @@ __global__ void halo_prime_kernel(SlabState* states, int depth) {
 // held by a running warp, so the launch needs neither co-residency of all CTAs nor a cooperative
 // launch.  Every wait is bounded by the slab's watchdog.
 __device__ __forceinline__ void red_release_gpu_add_u32(unsigned int* p, unsigned int v) {
+  if (!GOL_CHK(p, 4)) return;
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
@@ -970,7 +1020,8 @@ __global__ void __launch_bounds__(MAXT, MINB) life_flow_kernel(SlabState* states
       st->words_seen += nex * (unsigned long long)fp.depth * (unsigned long long)st->ws;
     }
     const int n = fp.nslabs * fp.max_strips;
-    for (int i = lane; i < n; i += 32) fp.progress[i] = 0u;
+    for (int i = lane; i < n; i += 32)
+      if (GOL_CHK(fp.progress + i, 4)) fp.progress[i] = 0u;
     __syncwarp();
     if (lane == 0) {
       fp.ctl[0] = 0u;
@@ -998,7 +1049,7 @@ __global__ void pattern_init_kernel(uint64_t* rows, int64_t stride, PatternArgs 
       const bool maybe = (y == 0 || y == a.H - 1) && (w <= 2 || w == ws - 1);
       v = maybe ? pattern_word(a, y, w) : 0ull;
     }
-    rows[y * stride + w] = v;
+    if (GOL_CHK(rows + y * stride + w, 8)) rows[y * stride + w] = v;
   }
 }
 
@@ -1026,6 +1077,7 @@ __global__ void pack_kernel(const uint8_t* __restrict__ cells, uint64_t* __restr
     const uint8_t* src = cells + y * W + w * 64;
     const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
     uint64_t v = 0;
+    if (!GOL_CHK(src, n) || !GOL_CHK(words + y * stride + w, 8)) continue;
     if (aligned && n == 64) {
       const uint64_t* s8 = (const uint64_t*)src;
 #pragma unroll
@@ -1045,9 +1097,11 @@ __global__ void unpack_kernel(const uint64_t* __restrict__ words, uint8_t* __res
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t y = i / ws, w = i - y * ws;
+    if (!GOL_CHK(words + y * stride + w, 8)) continue;
     const uint64_t v = il_to_std(words[y * stride + w]);   // storage layout -> column order
     uint8_t* dst = cells + y * W + w * 64;
     const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
+    if (!GOL_CHK(dst, n)) continue;
     if (aligned && n == 64) {
       uint64_t* d8 = (uint64_t*)dst;
 #pragma unroll
@@ -1065,6 +1119,7 @@ __global__ void __launch_bounds__(kPopThreads) population_partial_kernel(
   unsigned long long acc = 0;
   for (int64_t y = blockIdx.x; y < H; y += gridDim.x) {
     const uint64_t* row = words + y * stride;
+    if (!GOL_CHK(row, ws * 8)) continue;
     for (int64_t w = threadIdx.x; w < ws; w += blockDim.x) acc += (unsigned)__popcll(row[w]);
   }
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(kFull, acc, o);
@@ -1074,13 +1129,14 @@ __global__ void __launch_bounds__(kPopThreads) population_partial_kernel(
   if (threadIdx.x == 0) {
     unsigned long long t = 0;
     for (int i = 0; i < kPopThreads / 32; ++i) t += wsum[i];
-    partials[blockIdx.x] = t;
+    if (GOL_CHK(partials + blockIdx.x, 8)) partials[blockIdx.x] = t;
   }
 }
 
 __global__ void __launch_bounds__(kPopThreads) population_final_kernel(
     const unsigned long long* __restrict__ partials, int n, unsigned long long* __restrict__ out) {
   unsigned long long acc = 0;
+  if (!GOL_CHK(partials, (long long)n * 8) || !GOL_CHK(out, 8)) return;
   for (int i = threadIdx.x; i < n; i += blockDim.x) acc += partials[i];
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(kFull, acc, o);
   __shared__ unsigned long long wsum[kPopThreads / 32];
@@ -1106,8 +1162,13 @@ __global__ void format_rows_kernel(const uint64_t* __restrict__ rows, int64_t st
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / ws, w = i - r * ws;
+    if (!GOL_CHK(rows + r * stride + w, 8)) continue;
     const uint64_t v = il_to_std(rows[r * stride + w]);   // storage layout -> column order
     char* row_text = text + r * pitch;
+    // everything this thread may write: its cells, the newline (last word), the prefix (first word)
+    if (!GOL_CHK(row_text + kTextCellOff + w * 128, 2 * ((W - w * 64) < 64 ? (W - w * 64) : 64)) ||
+        (w == ws - 1 && !GOL_CHK(row_text + kTextCellOff + 2 * W, 1)) || (w == 0 && !GOL_CHK(row_text, kTextCellOff)))
+      continue;
     char* dst = row_text + kTextCellOff + w * 128;
     const int n = (int)((W - w * 64) < 64 ? (W - w * 64) : 64);
     if (n == 64) {
@@ -1167,7 +1228,8 @@ __global__ void step_rows_kernel(const uint64_t* __restrict__ in, uint64_t* __re
     const uint64_t* cur = in + y * stride;
     const uint64_t* up = (y == 0) ? top : cur - stride;
     const uint64_t* down = (y == H - 1) ? bottom : cur + stride;
-    out[y * stride + w] = step_word(up, cur, down, w, ws, W);
+    if (GOL_CHK(up, ws * 8) && GOL_CHK(cur, ws * 8) && GOL_CHK(down, ws * 8) && GOL_CHK(out + y * stride + w, 8))
+      out[y * stride + w] = step_word(up, cur, down, w, ws, W);
   }
 }
 
@@ -1216,6 +1278,80 @@ template <int K> const void* flow_fn() {
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------
+
+// ---- bounds-checking build: host side of the region registry -----------------------------------
+#if GOL_DEBUG_BOUNDS
+bool debug_bounds_enabled() { return true; }
+static int dbg_fetch(DebugRegions* h) { return cudaMemcpyFromSymbol(h, g_dbg, sizeof *h) == cudaSuccess ? 0 : -1; }
+static int dbg_store(const DebugRegions* h) { return cudaMemcpyToSymbol(g_dbg, h, sizeof *h) == cudaSuccess ? 0 : -1; }
+int debug_bounds_register(const void* p, size_t n) {
+  if (!p || !n) return 0;
+  cudaDeviceSynchronize();
+  DebugRegions h;
+  if (dbg_fetch(&h)) return -1;
+  const unsigned long long lo = (unsigned long long)p, hi = lo + n;
+  for (int i = 0; i < h.n; ++i)
+    if (h.lo[i] == lo) {   // same base again: keep the larger extent
+      if (hi > h.hi[i]) h.hi[i] = hi;
+      return dbg_store(&h);
+    }
+  if (h.n >= kDbgMaxRegions) return -1;
+  h.lo[h.n] = lo;
+  h.hi[h.n] = hi;
+  ++h.n;
+  return dbg_store(&h);
+}
+int debug_bounds_unregister(const void* p) {
+  if (!p) return 0;
+  cudaDeviceSynchronize();
+  DebugRegions h;
+  if (dbg_fetch(&h)) return -1;
+  for (int i = 0; i < h.n; ++i)
+    if (h.lo[i] == (unsigned long long)p) {
+      h.lo[i] = h.lo[h.n - 1];
+      h.hi[i] = h.hi[h.n - 1];
+      --h.n;
+      break;
+    }
+  return dbg_store(&h);
+}
+int debug_bounds_query(unsigned long long* violations, unsigned long long* first_bad, int* line, int reset) {
+  cudaDeviceSynchronize();
+  DebugRegions h;
+  if (dbg_fetch(&h)) return -1;
+  if (violations) *violations = h.violations;
+  if (first_bad) *first_bad = h.first_bad;
+  if (line) *line = h.first_line;
+  if (reset) {
+    h.violations = 0;
+    h.first_bad = 0;
+    h.first_line = 0;
+    return dbg_store(&h);
+  }
+  return 0;
+}
+namespace {
+__global__ void debug_poke_kernel(const uint64_t* p, uint64_t* sink) {
+  const uint64_t v = ld_cg(p);
+  if (sink && GOL_CHK(sink, 8)) *sink = v;
+}
+}  // namespace
+int debug_bounds_poke(const void* p) {
+  debug_poke_kernel<<<1, 1>>>((const uint64_t*)p, nullptr);
+  return cudaDeviceSynchronize() == cudaSuccess ? 0 : -1;
+}
+#else
+bool debug_bounds_enabled() { return false; }
+int debug_bounds_register(const void*, size_t) { return 0; }
+int debug_bounds_unregister(const void*) { return 0; }
+int debug_bounds_query(unsigned long long* violations, unsigned long long* first_bad, int* line, int) {
+  if (violations) *violations = 0;
+  if (first_bad) *first_bad = 0;
+  if (line) *line = 0;
+  return 0;
+}
+int debug_bounds_poke(const void*) { return 0; }
+#endif
 
 static uint64_t g_launches = 0;
 void count_launch(uint64_t n) { __atomic_fetch_add(&g_launches, n, __ATOMIC_RELAXED); }

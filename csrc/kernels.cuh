@@ -72,6 +72,14 @@ cudaError_t launch_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64
                              const uint64_t* d_bottom, int64_t W, int64_t H, int64_t stride,
                              int threads, cudaStream_t s);
 
+// Bounds-checking build (-DGOL_DEBUG_BOUNDS=1, libgol_b200_debug.so): registry of the address ranges
+// kernels may touch on the CURRENT device.  No-ops that report zero violations in the normal build.
+bool debug_bounds_enabled();
+int debug_bounds_register(const void* p, size_t n);
+int debug_bounds_unregister(const void* p);
+int debug_bounds_query(unsigned long long* violations, unsigned long long* first_bad, int* line, int reset);
+int debug_bounds_poke(const void* p);   // one checked load of *p (tests that the detector fires)
+
 void count_launch(uint64_t n);
 uint64_t launch_count_value();
 

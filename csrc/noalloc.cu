@@ -121,6 +121,11 @@ extern "C" int gol_cuda_run_torus_noalloc(uint64_t* d_a, uint64_t* d_b, int64_t 
   st.peer_flag[1] = st.flag[0];
   st.watchdog_ns = 10ull * 1000 * 1000 * 1000;
 
+  if (debug_bounds_enabled()) {   // bounds-checking build only: the registry is host-side bookkeeping
+    debug_bounds_register(scratch, GOL_NOALLOC_SCRATCH_BYTES);
+    debug_bounds_register(d_a, (size_t)H * (size_t)stride * 8);
+    debug_bounds_register(d_b, (size_t)H * (size_t)stride * 8);
+  }
   count_launch(1);
   noalloc_setup_kernel<<<1, 32, 0, s>>>(st, scratch);
   e = cudaGetLastError();

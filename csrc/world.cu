@@ -17,7 +17,11 @@
 
 #include <algorithm>
 #include <cmath>
+#include <condition_variable>
+#include <functional>
 #include <map>
+#include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -37,6 +41,7 @@ namespace {
   } while (0)
 
 constexpr uint32_t kBlobMagic = 0x474F4C42u;  // "GOLB"
+constexpr int kCanaryByte = 0xA5;
 
 struct ExportBlob {
   uint32_t magic;
@@ -55,8 +60,11 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct Slab {
   int rank = 0, device = 0, group = 0, index_in_group = 0;
-  char* base = nullptr;
+  char* base = nullptr;    // mailbox: flags + recv rows + flag-in-data rows (the only memory peers touch; IPC-exported)
   size_t bytes = 0;
+  char* grid = nullptr;    // both slab buffers (never touched by a peer: kept out of the exported allocation)
+  size_t grid_bytes = 0;
+  std::vector<std::pair<char*, size_t>> canaries;   // guard rows between / around every buffer
   size_t off_flags = 0, off_recv[2][2] = {{0, 0}, {0, 0}}, off_ll[2][2] = {{0, 0}, {0, 0}}, off_buf[2] = {0, 0};
   SlabState h{};
   unsigned long long* d_partials = nullptr;
@@ -88,8 +96,61 @@ struct PassItem {
   PassParams p{};
 };
 
+// One launch thread per device: a 257-node graph launch costs the host ~0.2 ms, and eight of them
+// issued one after the other from a single thread start the last GPU more than a millisecond
+// after the first - its ring neighbours then wait for it in every pass (171 instead of 235 TCUPS
+// on 8 GPUs from one process in round 1).  The reference gets the same effect from one MPI
+// process per rank (gol-main.c:58-62).
+struct Launcher {
+  std::thread th;
+  std::mutex m;
+  std::condition_variable cv;
+  std::function<cudaError_t()> job;
+  bool has_job = false, quit = false;
+  cudaError_t rc = cudaSuccess;
+
+  void run() {
+    std::unique_lock<std::mutex> lk(m);
+    for (;;) {
+      cv.wait(lk, [&] { return has_job || quit; });
+      if (quit) return;
+      std::function<cudaError_t()> j = job;
+      lk.unlock();
+      const cudaError_t r = j();
+      lk.lock();
+      rc = r;
+      has_job = false;
+      cv.notify_all();
+    }
+  }
+  void post(std::function<cudaError_t()> j) {
+    std::unique_lock<std::mutex> lk(m);
+    if (!th.joinable()) th = std::thread([this] { run(); });
+    cv.wait(lk, [&] { return !has_job; });
+    job = std::move(j);
+    has_job = true;
+    cv.notify_all();
+  }
+  cudaError_t wait() {
+    std::unique_lock<std::mutex> lk(m);
+    cv.wait(lk, [&] { return !has_job; });
+    return rc;
+  }
+  void stop() {
+    {
+      std::unique_lock<std::mutex> lk(m);
+      if (!th.joinable()) return;
+      cv.wait(lk, [&] { return !has_job; });
+      quit = true;
+      cv.notify_all();
+    }
+    th.join();
+  }
+};
+
 struct Group {
   int device = 0;
+  Launcher* launcher = nullptr;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   std::vector<int> slabs;
@@ -100,6 +161,7 @@ struct Group {
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   std::map<int64_t, std::pair<cudaGraphExec_t, int>> graphs;  // gens -> (exec, kernels)
   void* l2_policy_stream = nullptr;  // stream the L2 access-policy window was last applied to
+  bool l2_persist_held = false;      // this group holds a share of the device's persisting-L2 carve-out
 };
 
 struct Peer {
@@ -285,6 +347,7 @@ int finish_plan_cuda(gol_world* w) {
       const size_t n = g.slabs.size() * (size_t)w->flow_strips * sizeof(unsigned int);
       CU_TRY(cudaMalloc((void**)&g.d_progress, n));
       CU_TRY(cudaMemset(g.d_progress, 0, n));
+      debug_bounds_register(g.d_progress, n);
     }
   }
   return GOL_OK;
@@ -336,6 +399,7 @@ int make_tensor_maps(gol_world* w) {
       }
     }
     CU_TRY(cudaMalloc((void**)&g.d_tmaps, maps.size() * sizeof(CUtensorMap)));
+    debug_bounds_register(g.d_tmaps, maps.size() * sizeof(CUtensorMap));
     CU_TRY(cudaMemcpy(g.d_tmaps, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
   }
   return GOL_OK;
@@ -572,6 +636,31 @@ extern "C" {
 
 uint64_t gol_launch_count(void) { return launch_count_value(); }
 
+int gol_debug_bounds_enabled(void) { return debug_bounds_enabled() ? 1 : 0; }
+
+int gol_debug_bounds_report(uint64_t* violations, uint64_t* first_bad_address, int* source_line, int reset) {
+  unsigned long long n = 0, bad = 0;
+  int line = 0;
+  if (debug_bounds_query(&n, &bad, &line, reset)) return set_error(GOL_ERR_CUDA, "cannot read the bounds registry");
+  if (violations) *violations = n;
+  if (first_bad_address) *first_bad_address = bad;
+  if (source_line) *source_line = line;
+  return GOL_OK;
+}
+
+int gol_debug_bounds_poke(const void* device_address) {
+  return debug_bounds_poke(device_address) ? set_error(GOL_ERR_CUDA, "poke failed") : GOL_OK;
+}
+
+int gol_cuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
 gol_world_t* gol_world_create(const gol_config_t* cfg) {
   if (!cfg) {
     set_error(GOL_ERR_ARG, "null config");
@@ -650,30 +739,68 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
       set_error(GOL_ERR_CUDA, "cudaSetDevice(%d) failed", s.device);
       return fail();
     }
+    // Mailbox (the only memory ring neighbours write: flags, recv rows, flag-in-data rows; this
+    // is what gets exported over CUDA IPC) and grid (the two slab buffers) are separate
+    // allocations.  Every buffer is fenced by guard rows holding a fixed pattern, which
+    // gol_world_sync verifies on request (GOL_CHECK_CANARIES=1, always in the bounds-checking build).
+    const size_t guard = align_up(std::max<size_t>(row_bytes, 256), 256);
+    std::vector<size_t> mail_guards, grid_guards;
     size_t off = 0;
     s.off_flags = off;
     off += 256;
+    mail_guards.push_back(off);
+    off += guard;
     for (int side = 0; side < 2; ++side)
       for (int p = 0; p < 2; ++p) {
         s.off_recv[side][p] = off;
         off += recv_bytes;
+        mail_guards.push_back(off);
+        off += guard;
       }
     for (int side = 0; side < 2; ++side)
       for (int p = 0; p < 2; ++p) {   // flag-in-data halo rows: two 8-byte words per halo word
         s.off_ll[side][p] = off;
         off += 2 * recv_bytes;
+        mail_guards.push_back(off);
+        off += guard;
       }
-    for (int b = 0; b < 2; ++b) {
-      s.off_buf[b] = off;
-      off += buf_bytes;
-    }
     s.bytes = off;
+    s.grid_bytes = 0;
+    grid_guards.push_back(s.grid_bytes);
+    s.grid_bytes += guard;
+    for (int b = 0; b < 2; ++b) {
+      s.off_buf[b] = s.grid_bytes;
+      s.grid_bytes += buf_bytes;
+      grid_guards.push_back(s.grid_bytes);
+      s.grid_bytes += guard;
+    }
     e = cudaMalloc((void**)&s.base, s.bytes);
     if (e == cudaSuccess) e = cudaMemset(s.base, 0, s.bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&s.grid, s.grid_bytes);
+    if (e == cudaSuccess) e = cudaMemset(s.grid, 0, s.grid_bytes);
+    for (size_t o : mail_guards) {
+      if (e == cudaSuccess) e = cudaMemset(s.base + o, kCanaryByte, guard);
+      s.canaries.emplace_back(s.base + o, guard);
+    }
+    for (size_t o : grid_guards) {
+      if (e == cudaSuccess) e = cudaMemset(s.grid + o, kCanaryByte, guard);
+      s.canaries.emplace_back(s.grid + o, guard);
+    }
     if (e == cudaSuccess) e = cudaMalloc((void**)&s.d_partials, (kPopBlocks + 1) * sizeof(unsigned long long));
+    if (e == cudaSuccess) {
+      // bounds-checking build: each buffer is a region of its own, the guard rows belong to none
+      debug_bounds_register(s.base + s.off_flags, 256);
+      for (int side = 0; side < 2; ++side)
+        for (int p = 0; p < 2; ++p) {
+          debug_bounds_register(s.base + s.off_recv[side][p], recv_bytes);
+          debug_bounds_register(s.base + s.off_ll[side][p], 2 * recv_bytes);
+        }
+      for (int b = 0; b < 2; ++b) debug_bounds_register(s.grid + s.off_buf[b], buf_bytes);
+      debug_bounds_register(s.d_partials, (kPopBlocks + 1) * sizeof(unsigned long long));
+    }
     if (e != cudaSuccess) {
-      set_error(GOL_ERR_CUDA, "slab allocation of %zu bytes on device %d failed: %s", s.bytes, s.device,
-                cudaGetErrorString(e));
+      set_error(GOL_ERR_CUDA, "slab allocation of %zu bytes on device %d failed: %s", s.bytes + s.grid_bytes,
+                s.device, cudaGetErrorString(e));
       return fail();
     }
     s.d_pop = s.d_partials + kPopBlocks;
@@ -686,7 +813,7 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
     h.G = w->G;
     h.rank = s.rank;
     h.nranks = cfg->nranks;
-    for (int b = 0; b < 2; ++b) h.buf[b] = (uint64_t*)(s.base + s.off_buf[b]);
+    for (int b = 0; b < 2; ++b) h.buf[b] = (uint64_t*)(s.grid + s.off_buf[b]);
     for (int side = 0; side < 2; ++side)
       for (int p = 0; p < 2; ++p) {
         h.recv[side][p] = (uint64_t*)(s.base + s.off_recv[side][p]);
@@ -710,6 +837,10 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
     if (e == cudaSuccess) e = cudaMemset(g.d_barrier, 0, 256);
     if (e == cudaSuccess) e = cudaEventCreate(&g.e0);
     if (e == cudaSuccess) e = cudaEventCreate(&g.e1);
+    if (e == cudaSuccess) {
+      debug_bounds_register(g.d_states, g.slabs.size() * sizeof(SlabState));
+      debug_bounds_register(g.d_barrier, 256);
+    }
     if (e != cudaSuccess) {
       set_error(GOL_ERR_CUDA, "device %d set-up failed: %s", g.device, cudaGetErrorString(e));
       return fail();
@@ -720,15 +851,26 @@ gol_world_t* gol_world_create(const gol_config_t* cfg) {
   return w;
 }
 
+static void persist_release(int device);
+
 void gol_world_destroy(gol_world_t* w) {
   if (!w) return;
   if (w->cuda) {
     for (auto& g : w->groups) {
       cudaSetDevice(g.device);
       if (g.stream) cudaStreamSynchronize(g.stream);
+      if (g.l2_persist_held) persist_release(g.device);
+      if (g.launcher) {
+        g.launcher->stop();
+        delete g.launcher;
+        g.launcher = nullptr;
+      }
       for (auto& kv : g.graphs) cudaGraphExecDestroy(kv.second.first);
       if (g.e0) cudaEventDestroy(g.e0);
       if (g.e1) cudaEventDestroy(g.e1);
+      debug_bounds_unregister(g.d_states);
+      debug_bounds_unregister(g.d_barrier);
+      debug_bounds_unregister(g.d_progress);
       if (g.d_states) cudaFree(g.d_states);
       if (g.d_barrier) cudaFree(g.d_barrier);
       if (g.d_progress) cudaFree(g.d_progress);
@@ -742,7 +884,22 @@ void gol_world_destroy(gol_world_t* w) {
       }
     for (auto& s : w->slabs) {
       cudaSetDevice(s.device);
+      if (debug_bounds_enabled() && s.base) {
+        debug_bounds_unregister(s.base + s.off_flags);
+        for (int side = 0; side < 2; ++side)
+          for (int p = 0; p < 2; ++p) {
+            debug_bounds_unregister(s.base + s.off_recv[side][p]);
+            debug_bounds_unregister(s.base + s.off_ll[side][p]);
+          }
+        for (int b = 0; b < 2; ++b) debug_bounds_unregister(s.grid + s.off_buf[b]);
+        debug_bounds_unregister(s.d_partials);
+        for (int k = 0; k < 2; ++k) {
+          debug_bounds_unregister(s.stage_in[k]);
+          debug_bounds_unregister(s.stage_out[k]);
+        }
+      }
       if (s.base) cudaFree(s.base);
+      if (s.grid) cudaFree(s.grid);
       if (s.d_partials) cudaFree(s.d_partials);
       for (int k = 0; k < 2; ++k) {
         if (s.stage_in[k]) cudaFree(s.stage_in[k]);
@@ -923,6 +1080,20 @@ int gol_world_connect(gol_world_t* w) {
     if (rc) return rc;
     rc = resolve_peer_base(w, next, s.device, &nb, &nl);
     if (rc) return rc;
+    if (debug_bounds_enabled()) {
+      // the neighbours' mailboxes as seen from this device (same geometry, hence same sizes)
+      CU_TRY(cudaSetDevice(s.device));
+      const size_t recv_bytes = align_up((size_t)w->G * (size_t)w->stride * 8, 256);
+      for (int side = 0; side < 2; ++side)
+        for (int p = 0; p < 2; ++p) {
+          debug_bounds_register(pb + pl.off_recv[side][p], recv_bytes);
+          debug_bounds_register(pb + pl.off_ll[side][p], 2 * recv_bytes);
+          debug_bounds_register(nb + nl.off_recv[side][p], recv_bytes);
+          debug_bounds_register(nb + nl.off_ll[side][p], 2 * recv_bytes);
+        }
+      debug_bounds_register(pb + pl.off_flags, 256);
+      debug_bounds_register(nb + nl.off_flags, 256);
+    }
     for (int p = 0; p < 2; ++p) {
       s.h.peer_recv[0][p] = (uint64_t*)(pb + pl.off_recv[1][p]);  // prev's bottom recv
       s.h.peer_recv[1][p] = (uint64_t*)(nb + nl.off_recv[0][p]);  // next's top recv
@@ -1019,9 +1190,11 @@ int gol_world_load_bytes(gol_world_t* w, int li, const uint8_t* cells) {
   uint8_t* d = nullptr;
   const size_t n = (size_t)w->W * (size_t)w->H;
   CU_TRY(cudaMalloc((void**)&d, n));
+  debug_bounds_register(d, n);
   cudaError_t e = cudaMemcpyAsync(d, cells, n, cudaMemcpyHostToDevice, g.stream);
   if (e == cudaSuccess) e = launch_pack(d, cur_interior(w, s), w->W, w->H, w->stride, g.stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  debug_bounds_unregister(d);
   cudaFree(d);
   if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "load_bytes: %s", cudaGetErrorString(e));
   return GOL_OK;
@@ -1075,6 +1248,8 @@ static int pipeline_prepare(gol_world* w, Slab& s) {
   for (int k = 0; k < 2; ++k) {
     CU_TRY(cudaMalloc((void**)&s.stage_in[k], n));
     CU_TRY(cudaMalloc((void**)&s.stage_out[k], n));
+    debug_bounds_register(s.stage_in[k], n);
+    debug_bounds_register(s.stage_out[k], n);
     CU_TRY(cudaEventCreateWithFlags(&s.ev_h2d[k], cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&s.ev_in_used[k], cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&s.ev_out[k], cudaEventDisableTiming));
@@ -1176,9 +1351,11 @@ int gol_world_read_bytes(gol_world_t* w, int li, uint8_t* cells) {
   uint8_t* d = nullptr;
   const size_t n = (size_t)w->W * (size_t)w->H;
   CU_TRY(cudaMalloc((void**)&d, n));
+  debug_bounds_register(d, n);
   cudaError_t e = launch_unpack(cur_interior(w, s), d, w->W, w->H, w->stride, g.stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(cells, d, n, cudaMemcpyDeviceToHost, g.stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  debug_bounds_unregister(d);
   cudaFree(d);
   if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "read_bytes: %s", cudaGetErrorString(e));
   return GOL_OK;
@@ -1214,7 +1391,22 @@ int gol_world_population(gol_world_t* w, int li, uint64_t* out) {
 // L2 residency control: mark the slab allocation of every slab on this device as "persisting" in
 // L2 for kernels launched on the group's stream, so that streaming traffic (the end-to-end
 // pipeline's PCIe uploads / downloads, which pass through L2) evicts itself instead of the
-// double buffer the step kernels live in.  GOL_L2_PERSIST=0 disables it.
+// double buffer the step kernels live in, and a step that starts on a cold or dirty L2 (another
+// kernel ran in between) gets its working set resident within a pass or two: 8.05 instead of
+// 8.7 ms per 1024 generations at 16384^2 after a 256 MiB write.  The carve-out is a device-wide
+// limit: it is counted per device and given back when the last world using it goes away (left
+// set, a later world whose slab does not fit ran at 31.6 instead of 40.5 TCUPS on 65536 x 32768).
+// GOL_L2_PERSIST=0 disables it.
+static int g_persist_users[64];
+static void persist_release(int device) {
+  if (device < 0 || device >= 64 || g_persist_users[device] <= 0) return;
+  if (--g_persist_users[device] == 0) {
+    cudaSetDevice(device);
+    cudaCtxResetPersistingL2Cache();
+    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0);
+    cudaGetLastError();
+  }
+}
 static int apply_l2_policy(gol_world* w, Group& g) {
   static const int enabled = getenv("GOL_L2_PERSIST") ? atoi(getenv("GOL_L2_PERSIST")) : 1;
   if (!enabled || g.l2_policy_stream == (void*)g.stream) return GOL_OK;
@@ -1228,16 +1420,21 @@ static int apply_l2_policy(gol_world* w, Group& g) {
   char* hi = nullptr;
   for (int si : g.slabs) {
     Slab& s = w->slabs[(size_t)si];
-    if (!lo || s.base < lo) lo = s.base;
-    if (!hi || s.base + s.bytes > hi) hi = s.base + s.bytes;
+    if (!lo || s.grid < lo) lo = s.grid;
+    if (!hi || s.grid + s.grid_bytes > hi) hi = s.grid + s.grid_bytes;
   }
   size_t span = (size_t)(hi - lo);
   // a window larger than the carve-out would demote part of the double buffer to "streaming":
   // measured 30.7 vs 34.8 TCUPS on a 16384 x 32768 slab (128 MiB), so only slabs that fit are pinned
   if (span > (size_t)max_window || span > (size_t)max_persist) return GOL_OK;
-  if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist) != cudaSuccess) {
-    cudaGetLastError();
-    return GOL_OK;
+  if (g.device >= 64) return GOL_OK;
+  if (!g.l2_persist_held) {
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist) != cudaSuccess) {
+      cudaGetLastError();
+      return GOL_OK;
+    }
+    g.l2_persist_held = true;
+    ++g_persist_users[g.device];
   }
   cudaStreamAttrValue v;
   memset(&v, 0, sizeof v);
@@ -1377,10 +1574,29 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
       int rc = get_graph(w, g, todo, items, &ge);
       if (rc) return rc;
       if (!launch) continue;
-      CU_TRY(cudaGraphLaunch(ge->first, g.stream));
+      if (w->groups.size() > 1) {
+        // all devices' graphs leave at the same time, each from its own thread
+        if (!g.launcher) g.launcher = new Launcher();
+        const int dev = g.device;
+        cudaGraphExec_t exec = ge->first;
+        cudaStream_t st = g.stream;
+        g.launcher->post([dev, exec, st]() -> cudaError_t {
+          cudaError_t e = cudaSetDevice(dev);
+          return e != cudaSuccess ? e : cudaGraphLaunch(exec, st);
+        });
+      } else {
+        CU_TRY(cudaGraphLaunch(ge->first, g.stream));
+      }
       count_launch((uint64_t)ge->second);
     }
     if (!launch) return GOL_OK;
+    if (w->groups.size() > 1)
+      for (auto& g : w->groups)
+        if (g.launcher) {
+          const cudaError_t e = g.launcher->wait();
+          if (e != cudaSuccess)
+            return set_error(GOL_ERR_CUDA, "graph launch on device %d failed: %s", g.device, cudaGetErrorString(e));
+        }
   } else {
     if (!launch) return GOL_OK;
     for (auto& item : items)
@@ -1423,6 +1639,24 @@ int gol_world_step(gol_world_t* w, int64_t gens) {
   return rc;
 }
 
+// Guard rows around every buffer must still hold their pattern (a kernel that ran past the end of
+// a slab buffer, a recv buffer or a flag-in-data buffer lands in one first).
+static int check_canaries(gol_world* w) {
+  std::vector<unsigned char> h;
+  for (auto& s : w->slabs) {
+    CU_TRY(cudaSetDevice(s.device));
+    for (size_t i = 0; i < s.canaries.size(); ++i) {
+      h.resize(s.canaries[i].second);
+      CU_TRY(cudaMemcpy(h.data(), s.canaries[i].first, h.size(), cudaMemcpyDeviceToHost));
+      for (size_t b = 0; b < h.size(); ++b)
+        if (h[b] != (unsigned char)kCanaryByte)
+          return set_error(GOL_ERR_STATE, "rank %d: guard row %zu was overwritten at byte %zu (a kernel wrote outside "
+                           "its buffer)", s.rank, i, b);
+    }
+  }
+  return GOL_OK;
+}
+
 int gol_world_sync(gol_world_t* w) {
   if (!w) return set_error(GOL_ERR_ARG, "null world");
   if (!w->cuda) return GOL_OK;
@@ -1430,6 +1664,23 @@ int gol_world_sync(gol_world_t* w) {
     CU_TRY(cudaSetDevice(g.device));
     CU_TRY(cudaStreamSynchronize(g.stream));
   }
+  {
+    const char* e = getenv("GOL_CHECK_CANARIES");
+    if (debug_bounds_enabled() || (e && atoi(e))) {
+      int rc = check_canaries(w);
+      if (rc) return rc;
+    }
+  }
+  if (debug_bounds_enabled())
+    for (auto& g : w->groups) {
+      CU_TRY(cudaSetDevice(g.device));
+      unsigned long long n = 0, bad = 0;
+      int line = 0;
+      debug_bounds_query(&n, &bad, &line, 0);
+      if (n)
+        return set_error(GOL_ERR_STATE, "device %d: %llu out-of-bounds accesses, first at %#llx (csrc/kernels.cu:%d)",
+                         g.device, n, bad, line);
+    }
   for (auto& g : w->groups) {
     CU_TRY(cudaSetDevice(g.device));
     std::vector<SlabState> hs(g.slabs.size());
@@ -1571,6 +1822,8 @@ int gol_world_dump_text(gol_world_t* w, int li, const char* dir) {
   char* d_text = nullptr;
   char* h_text = nullptr;
   CU_TRY(cudaMalloc((void**)&d_text, (size_t)(chunk_rows * pitch)));
+  debug_bounds_register(d_text, (size_t)(chunk_rows * pitch));
+  struct Unreg { char* p; ~Unreg() { debug_bounds_unregister(p); } } unreg{d_text};
   cudaError_t e = cudaMallocHost((void**)&h_text, (size_t)(chunk_rows * pitch));
   if (e != cudaSuccess) {
     cudaFree(d_text);
@@ -1615,12 +1868,16 @@ int gol_world_dump_text(gol_world_t* w, int li, const char* dir) {
 // ---- stateless device ops -------------------------------------------------------
 int gol_cuda_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H, void* stream) {
   if (!d_cells || !d_words || W < 1 || H < 1) return set_error(GOL_ERR_ARG, "gol_cuda_pack: bad argument");
+  debug_bounds_register(d_cells, (size_t)W * (size_t)H);
+  debug_bounds_register(d_words, (size_t)H * (size_t)row_stride_words(W) * 8);
   CU_TRY(launch_pack(d_cells, d_words, W, H, row_stride_words(W), (cudaStream_t)stream));
   return GOL_OK;
 }
 
 int gol_cuda_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H, void* stream) {
   if (!d_cells || !d_words || W < 1 || H < 1) return set_error(GOL_ERR_ARG, "gol_cuda_unpack: bad argument");
+  debug_bounds_register(d_cells, (size_t)W * (size_t)H);
+  debug_bounds_register(d_words, (size_t)H * (size_t)row_stride_words(W) * 8);
   CU_TRY(launch_unpack(d_words, d_cells, W, H, row_stride_words(W), (cudaStream_t)stream));
   return GOL_OK;
 }
@@ -1631,6 +1888,9 @@ int gol_cuda_population(const uint64_t* d_words, int64_t W, int64_t H, void* d_s
                         void* stream) {
   if (!d_words || !d_scratch || !d_out || W < 1 || H < 1)
     return set_error(GOL_ERR_ARG, "gol_cuda_population: bad argument");
+  debug_bounds_register(d_words, (size_t)H * (size_t)row_stride_words(W) * 8);
+  debug_bounds_register(d_scratch, gol_cuda_population_scratch_bytes());
+  debug_bounds_register(d_out, 8);
   CU_TRY(launch_population(d_words, words_per_row(W), row_stride_words(W), H, (unsigned long long*)d_scratch,
                            (unsigned long long*)d_out, (cudaStream_t)stream));
   return GOL_OK;
@@ -1642,6 +1902,8 @@ int gol_cuda_step_torus(const uint64_t* d_in, uint64_t* d_out, int64_t W, int64_
   if (threads <= 0) threads = 256;
   if (threads > 1024) return set_error(GOL_ERR_ARG, "threads per block must be <= 1024");
   const int64_t st = row_stride_words(W);
+  debug_bounds_register(d_in, (size_t)H * (size_t)st * 8);
+  debug_bounds_register(d_out, (size_t)H * (size_t)st * 8);
   CU_TRY(launch_step_rows(d_in, d_out, d_in + (H - 1) * st, d_in, W, H, st, threads, (cudaStream_t)stream));
   return GOL_OK;
 }
@@ -1652,6 +1914,10 @@ int gol_cuda_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_
     return set_error(GOL_ERR_ARG, "gol_cuda_step_rows: bad argument");
   if (threads <= 0) threads = 256;
   if (threads > 1024) return set_error(GOL_ERR_ARG, "threads per block must be <= 1024");
+  debug_bounds_register(d_in, (size_t)H * (size_t)row_stride_words(W) * 8);
+  debug_bounds_register(d_out, (size_t)H * (size_t)row_stride_words(W) * 8);
+  debug_bounds_register(d_top, (size_t)row_stride_words(W) * 8);
+  debug_bounds_register(d_bottom, (size_t)row_stride_words(W) * 8);
   CU_TRY(launch_step_rows(d_in, d_out, d_top, d_bottom, W, H, row_stride_words(W), threads, (cudaStream_t)stream));
   return GOL_OK;
 }

@@ -16,7 +16,9 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-_LIB_PATH = os.path.join(_HERE, "_lib", "libgol_b200.so")
+# GOL_B200_LIB=debug loads the bounds-checking build (libgol_b200_debug.so, -DGOL_DEBUG_BOUNDS=1)
+_LIB_PATH = os.path.join(_HERE, "_lib", "libgol_b200_debug.so" if os.environ.get("GOL_B200_LIB") == "debug"
+                         else "libgol_b200.so")
 
 BACKEND_CPU, BACKEND_CUDA = 0, 1
 MODES = {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4}
@@ -72,6 +74,10 @@ def _load() -> C.CDLL:
     sigs = {
         "gol_last_error": (C.c_char_p, []),
         "gol_version": (C.c_char_p, []),
+        "gol_cuda_device_count": (I32, []),
+        "gol_debug_bounds_enabled": (I32, []),
+        "gol_debug_bounds_report": (I32, [P(U64), P(U64), P(I32), I32]),
+        "gol_debug_bounds_poke": (I32, [VP]),
         "gol_oracle_run": (I32, [VP, VP, I64, I64, I64]),
         "gol_pattern_fill_bytes": (I32, [VP, I32, I64, I64, I32, I32, U64, C.c_double]),
         "gol_words_per_row": (I64, [I64]),
@@ -140,6 +146,17 @@ def check(rc: int) -> None:
 
 def version() -> str:
     return lib.gol_version().decode()
+
+
+def debug_bounds_enabled() -> bool:
+    """True when the loaded library is the bounds-checking build (``GOL_B200_LIB=debug``)."""
+    return bool(lib.gol_debug_bounds_enabled())
+
+
+def debug_bounds_report(reset: bool = False) -> dict:
+    n, bad, line = C.c_uint64(0), C.c_uint64(0), C.c_int(0)
+    check(lib.gol_debug_bounds_report(C.byref(n), C.byref(bad), C.byref(line), int(reset)))
+    return {"violations": int(n.value), "first_bad_address": int(bad.value), "source_line": int(line.value)}
 
 
 def launch_count() -> int:

@@ -43,6 +43,15 @@ class Life:
             self.nranks = dist.get_world_size()
             self.rank = dist.get_rank()
             local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+            if backend == "cuda":
+                ndev = int(_native.lib.gol_cuda_device_count())
+                local_world = int(os.environ.get("LOCAL_WORLD_SIZE", self.nranks))
+                if ndev < min(local_world, self.nranks):
+                    # kernels of two processes that wait on each other's halo flags must not share a GPU:
+                    # nothing guarantees that both are resident at the same time
+                    raise _native.GolError(f"{min(local_world, self.nranks)} ranks on this node but only {ndev} "
+                                           "GPU(s): the process-per-GPU model needs one GPU per rank "
+                                           "(use Life(..., ranks=R) to host several ranks per GPU in one process)")
             self.world = World(self.width, self.rows, nranks=self.nranks, first_rank=self.rank, nlocal=1,
                                backend=backend, mode=mode, k=k, depth=depth, threads=threads,
                                device_base=local_rank, flags=flags)

@@ -45,6 +45,20 @@ extern "C" {
 
 const char* gol_last_error(void);
 const char* gol_version(void);
+/* Memory-safety build.  libgol_b200_debug.so is the same library compiled with
+ * -DGOL_DEBUG_BOUNDS=1: every global load / store / atomic of every kernel first checks its address
+ * range against a registry of the buffers the library allocated or was handed (each slab buffer,
+ * recv buffer, flag ...; the guard rows between them belong to no region).  Misses are counted
+ * and skipped; gol_world_sync fails when there are any, and also verifies the guard rows.
+ * gol_debug_bounds_enabled(): 1 in that build, 0 in the normal one (where the report is always
+ * zero).  The report is for the current CUDA device; _poke performs one checked 8-byte load of the
+ * given device address (to test the detector).  The reference has no counterpart (SURVEY.md
+ * section 5: no sanitizers, no error checks beyond device binding). */
+int gol_debug_bounds_enabled(void);
+int gol_debug_bounds_report(uint64_t* violations, uint64_t* first_bad_address, int* source_line, int reset);
+int gol_debug_bounds_poke(const void* device_address);
+/* CUDA devices visible to this process (0 when there is no driver / device). */
+int gol_cuda_device_count(void);
 
 /* ---- CPU oracle and helpers (no GPU needed) ------------------------------ */
 

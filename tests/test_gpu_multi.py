@@ -55,3 +55,31 @@ def test_process_per_gpu_over_cuda_ipc():
            os.path.join(ROOT, "tests", "mp_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "MP_WORKER_OK" in r.stdout, (r.stdout[-2000:] + r.stderr[-4000:])
+
+
+def test_native_cli_process_per_rank_and_thread_per_device(tmp_path):
+    """bin/gol --spawn R: one native process per rank (fork, export blobs through shared memory,
+    CUDA-IPC mapping), the reference's process model (gol-main.c:58-62) without Python or MPI.
+    Its rank files must be byte-identical to the single-process run's (--ranks R: one launch
+    thread per device), and both must pass the oracle check."""
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    R = min(ngpu(), 4)
+    exe = os.path.join(ROOT, "bin", "gol")
+    outs = []
+    for flag in ("--spawn", "--ranks"):
+        d = tmp_path / flag.strip("-")
+        d.mkdir()
+        r = subprocess.run([exe, "6", "1024", "53", "256", "1", "--rows", "192", flag, str(R), "--check", "--outdir", str(d)],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and "CHECK: OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+        assert r.stdout.count("TOTAL DURATION") == 1
+        outs.append([(d / f"Rank_{i}_of_{R}.txt").read_bytes() for i in range(R)])
+    assert outs[0] == outs[1]
+
+
+def test_native_spawn_refuses_to_share_a_gpu():
+    exe = os.path.join(ROOT, "bin", "gol")
+    r = subprocess.run([exe, "6", "256", "8", "256", "0", "--spawn", str(ngpu() + 1)], capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 255 and "one GPU per rank" in r.stderr
