@@ -190,6 +190,7 @@ struct gol_world {
   uint64_t pass_host = 0;  // passes enqueued so far (buffer parity of every slab)
   int resident_warps = 0, sms = 0;
   int flow_strips = 0;     // strips per slab of the flow kernel (fixed for the world)
+  int flow_owner = 0;      // flow kernel: fixed owners (small slabs) instead of tickets
   int pipe_slot = 0;       // next slot of the end-to-end pipeline
 };
 
@@ -326,12 +327,24 @@ int finish_plan_cuda(gol_world* w) {
   const int cg_eff = p.mode == GOL_MODE_TMA ? (p.col_groups + tw - 1) / tw * tw : p.col_groups;
   p.strip_rows = pick_strip_rows(interior, cg_eff, p.temporal_k, slots, w->sms);
   if (p.mode == GOL_MODE_PERSISTENT) {
-    // The flow kernel hands tickets to free warps: it wants about three tasks per resident warp and
-    // pass so that a free warp always finds one whose neighbours are done, but not strips so short
-    // that the 2K pipeline-fill rows dominate (measured on B200: 36 rows at 16384^2, 64 at
-    // 65536 x 8192, 128 at 131072 x 16384, 256 at 65536^2; profiles/flow_kernel.md).
-    const int64_t per_warp = interior * cg_eff / (3 * (int64_t)std::max(1, slots));
-    p.strip_rows = (int)std::max<int64_t>(std::max(9 * p.temporal_k, p.exchange_depth), (per_warp + 3) / 4 * 4);
+    if (p.strip_rows < 8 * p.temporal_k && w->cfg.threads_per_block <= 0) {
+      // Small slab (one wave of resident warps already means strips of a few dozen rows): the
+      // run is bound by the per-pass hand-off between neighbouring strips, not by throughput.
+      // One warp per scheduler that owns its strip for the whole launch did best on a 4096^2
+      // slab (8.2 ms per 4096 generations; tickets 9.9 ms, graph of per-pass launches 9.7 ms).
+      w->flow_owner = 1;
+      p.threads_per_block = 128;
+      const int64_t warps = (int64_t)w->sms * 4 / std::max(1, slabs_per_dev);
+      const int64_t strips = std::max<int64_t>(1, warps / cg_eff - 2);
+      p.strip_rows = (int)std::max<int64_t>(2 * p.temporal_k, (interior + strips - 1) / strips);
+    } else {
+      // The flow kernel hands tickets to free warps: it wants about three tasks per resident warp
+      // and pass so that a free warp always finds one whose neighbours are done, but not strips so
+      // short that the 2K pipeline-fill rows dominate (measured on B200: 36 rows at 16384^2, 64 at
+      // 65536 x 8192, 128 at 131072 x 16384, 256 at 65536^2; profiles/flow_kernel.md).
+      const int64_t per_warp = interior * cg_eff / (3 * (int64_t)std::max(1, slots));
+      p.strip_rows = (int)std::max<int64_t>(std::max(9 * p.temporal_k, p.exchange_depth), (per_warp + 3) / 4 * 4);
+    }
     if (p.strip_rows > interior) p.strip_rows = (int)interior;
   }
   if (w->cfg.reserved > 0) p.strip_rows = w->cfg.reserved;   // explicit strip height (tuning / experiments)
@@ -1535,6 +1548,7 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
           fp.max_strips = nstrips;
           fp.ctl = g.d_barrier;
           fp.progress = g.d_progress;
+          fp.flags = w->flow_owner ? 4 : 0;
           if (const char* e = getenv("GOL_FLOW_FLAGS")) fp.flags = atoi(e);
           const int64_t tpp = (int64_t)fp.nslabs * nstrips * pl.col_groups;
           int nctas = flow_max_ctas(K, pl.threads_per_block, g.device);
