@@ -133,7 +133,7 @@ def reference_measure(args) -> dict:
     n = args.gpus
     width, rows, scaling = geometry(args, n)
     gens = args.gens
-    budget = float(os.environ.get("GOL_REF_BUDGET_S", "1500"))
+    budget = float(os.environ.get("GOL_REF_BUDGET_S", "1000"))   # wall-clock seconds for the timed reference steps
     noprintf = args.ref_variant == "noprintf"
     if scaling == "strong":
         # the reference CLI only knows square slabs (gol-main.c:76); the rectangular variant passes
@@ -158,10 +158,12 @@ def reference_measure(args) -> dict:
             # calibrate: a short run gives the per-generation cost, warm-up runs are short as well
             # (every step is a fresh process, there is no state to warm)
             cal_gens = 8
-            t_cal, _ = _ref_run(n, exe, pattern, width, cal_gens, 900, rows if scaling == "strong" else 0)
-            for _ in range(max(0, args.warmup - 1)):
+            t_cal, wall_cal = _ref_run(n, exe, pattern, width, cal_gens, 900, rows if scaling == "strong" else 0)
+            for _ in range(max(0, min(args.warmup, 2) - 1)):
                 _ref_run(n, exe, pattern, width, cal_gens, 900, rows if scaling == "strong" else 0)
-            est = t_cal / cal_gens * gens * 1.15 + 3.0
+            # a step costs the process start-up (managed allocation, host-side pattern fill: 10-17 s with
+            # eight ranks) plus the generation loop
+            est = (wall_cal - t_cal) + t_cal / cal_gens * gens * 1.1 + 1.0
             steps_run = int(max(1, min(args.steps, budget // est)))
             timer_s = wall_s = 0.0
             t_lo = time.time()

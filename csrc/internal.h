@@ -176,4 +176,18 @@ struct FlowParams {
   unsigned int* progress; // [nslabs][max_strips] column-group tasks completed per strip in this launch
 };
 
+// Baked per launch of the resident kernel (small slabs that fit in shared memory, one CTA per strip,
+// thread-block clusters): the whole step() of `gens` generations in one launch.
+struct ResidentParams {
+  int32_t K;               // generations per halo exchange (halo depth)
+  int32_t npasses;         // ceil(gens / K)
+  int32_t last_k;          // generations of the last pass (1..K)
+  int32_t nslabs, ctas_per_slab, cluster;
+  int32_t rows_alloc;      // shared-memory rows per buffer: max strip rows + 2K
+  int32_t use_bulk;        // strips are loaded / stored with cp.async.bulk (rows are contiguous: stride == ws)
+  uint64_t* mail;          // CTA-to-CTA halo mailboxes in global memory (flag-in-data words)
+  int64_t mail_slot;       // words per (cta, side, parity) slot = 2 * K * ws
+  unsigned int* ctl;       // [1]: CTAs finished (the last one advances the slab counters)
+};
+
 }  // namespace gol

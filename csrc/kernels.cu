@@ -1504,10 +1504,16 @@ cudaError_t launch_flow(int K, SlabState* d_states, const FlowParams& fp0, int t
   return cudaLaunchKernel(fn, dim3((unsigned)nctas), dim3((unsigned)threads), args, 0, s);
 }
 
+// Grid of a grid-stride helper kernel: enough blocks for the data, at most 32 per SM of the
+// current device.
 static int grid_for(int64_t total, int threads) {
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+      sms < 1)
+    sms = 128;
   int64_t b = (total + threads - 1) / threads;
   if (b < 1) b = 1;
-  if (b > 148 * 32) b = 148 * 32;
+  if (b > (int64_t)sms * 32) b = (int64_t)sms * 32;
   return (int)b;
 }
 

@@ -57,7 +57,7 @@ cudaError_t launch_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, in
                         int64_t stride, cudaStream_t s);
 cudaError_t launch_unpack(const uint64_t* d_words, uint8_t* d_cells, int64_t W, int64_t H,
                           int64_t stride, cudaStream_t s);
-constexpr int kPopBlocks = 1184;  // 8 x 148
+constexpr int kPopBlocks = 1184;  // fixed (it sizes the caller-visible scratch); rows are taken grid-stride, any SM count
 constexpr int kPopThreads = 256;
 cudaError_t launch_population(const uint64_t* d_words, int64_t ws, int64_t stride, int64_t H,
                               unsigned long long* d_partials /* kPopBlocks */,

@@ -12,6 +12,7 @@
 // 64 and the grid is tall enough, life_generic otherwise) launched through the same
 // wrappers as everywhere else; only the home of their scratch differs.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include "../include/gol_b200.h"
 #include "internal.h"
@@ -119,7 +120,12 @@ extern "C" int gol_cuda_run_torus_noalloc(uint64_t* d_a, uint64_t* d_b, int64_t 
   }
   st.peer_flag[0] = st.flag[1];
   st.peer_flag[1] = st.flag[0];
-  st.watchdog_ns = 10ull * 1000 * 1000 * 1000;
+  {
+    // same knob as gol_world_create: how long a kernel waits for halo words before giving up
+    const char* e = getenv("GOL_WATCHDOG_MS");
+    const unsigned long long ms = e && atoll(e) > 0 ? (unsigned long long)atoll(e) : 10000ull;
+    st.watchdog_ns = ms * 1000ull * 1000ull;
+  }
 
   if (debug_bounds_enabled()) {   // bounds-checking build only: the registry is host-side bookkeeping
     debug_bounds_register(scratch, GOL_NOALLOC_SCRATCH_BYTES);

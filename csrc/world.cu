@@ -1192,6 +1192,13 @@ int gol_world_load_packed(gol_world_t* w, int li, const uint64_t* words) {
   return GOL_OK;
 }
 
+// Byte-cell I/O goes through a bounded device scratch (at most 64 MiB of byte cells at a time), so
+// that a 2^32-cell slab does not need 4 GiB of extra device memory to be loaded or read.
+static int64_t byte_io_chunk_rows(const gol_world* w) {
+  const int64_t rows = (int64_t)(64ll << 20) / std::max<int64_t>(1, w->W);
+  return std::max<int64_t>(1, std::min<int64_t>(rows, w->H));
+}
+
 int gol_world_load_bytes(gol_world_t* w, int li, const uint8_t* cells) {
   int rc = check_local(w, li);
   if (rc) return rc;
@@ -1200,13 +1207,19 @@ int gol_world_load_bytes(gol_world_t* w, int li, const uint8_t* cells) {
   if (!w->cuda) return gol_pack_bytes(cells, s.cbuf[s.ccur].data(), w->W, w->H);
   Group& g = w->groups[(size_t)s.group];
   CU_TRY(cudaSetDevice(s.device));
+  const int64_t chunk = byte_io_chunk_rows(w);
   uint8_t* d = nullptr;
-  const size_t n = (size_t)w->W * (size_t)w->H;
+  const size_t n = (size_t)w->W * (size_t)chunk;
   CU_TRY(cudaMalloc((void**)&d, n));
   debug_bounds_register(d, n);
-  cudaError_t e = cudaMemcpyAsync(d, cells, n, cudaMemcpyHostToDevice, g.stream);
-  if (e == cudaSuccess) e = launch_pack(d, cur_interior(w, s), w->W, w->H, w->stride, g.stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  cudaError_t e = cudaSuccess;
+  for (int64_t y0 = 0; y0 < w->H && e == cudaSuccess; y0 += chunk) {
+    const int64_t rows = std::min(chunk, w->H - y0);
+    e = cudaMemcpyAsync(d, cells + (size_t)y0 * (size_t)w->W, (size_t)rows * (size_t)w->W, cudaMemcpyHostToDevice,
+                        g.stream);
+    if (e == cudaSuccess) e = launch_pack(d, cur_interior(w, s) + y0 * w->stride, w->W, rows, w->stride, g.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);   // the scratch is reused by the next chunk
+  }
   debug_bounds_unregister(d);
   cudaFree(d);
   if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "load_bytes: %s", cudaGetErrorString(e));
@@ -1361,13 +1374,20 @@ int gol_world_read_bytes(gol_world_t* w, int li, uint8_t* cells) {
   if (!w->cuda) return gol_unpack_words(s.cbuf[s.ccur].data(), cells, w->W, w->H);
   Group& g = w->groups[(size_t)s.group];
   CU_TRY(cudaSetDevice(s.device));
+  const int64_t chunk = byte_io_chunk_rows(w);
   uint8_t* d = nullptr;
-  const size_t n = (size_t)w->W * (size_t)w->H;
+  const size_t n = (size_t)w->W * (size_t)chunk;
   CU_TRY(cudaMalloc((void**)&d, n));
   debug_bounds_register(d, n);
-  cudaError_t e = launch_unpack(cur_interior(w, s), d, w->W, w->H, w->stride, g.stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(cells, d, n, cudaMemcpyDeviceToHost, g.stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  cudaError_t e = cudaSuccess;
+  for (int64_t y0 = 0; y0 < w->H && e == cudaSuccess; y0 += chunk) {
+    const int64_t rows = std::min(chunk, w->H - y0);
+    e = launch_unpack(cur_interior(w, s) + y0 * w->stride, d, w->W, rows, w->stride, g.stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(cells + (size_t)y0 * (size_t)w->W, d, (size_t)rows * (size_t)w->W, cudaMemcpyDeviceToHost,
+                          g.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+  }
   debug_bounds_unregister(d);
   cudaFree(d);
   if (e != cudaSuccess) return set_error(GOL_ERR_CUDA, "read_bytes: %s", cudaGetErrorString(e));

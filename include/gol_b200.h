@@ -266,6 +266,11 @@ int gol_cuda_step_rows(const uint64_t* d_in, uint64_t* d_out, const uint64_t* d_
  *    call left in it; each call re-initialises the counters and flags it needs.  Two calls
  *    whose GPU work can overlap (different streams, no dependency) corrupt each other:
  *    serialise them.
+ *  - A device-side wait that runs into the watchdog (GOL_WATCHDOG_MS, default 10 s; in practice
+ *    only when two overlapping calls trample each other's flags) is NOT reported by this call:
+ *    it returns as soon as the work is enqueued, and the scratch header that records the
+ *    failure is rewritten by the next call.  Callers that overlap calls get wrong cells, not an
+ *    error code.
  */
 #define GOL_NOALLOC_MAX_WIDTH 131072
 #define GOL_NOALLOC_SCRATCH_BYTES (272 * 1024)
