@@ -466,11 +466,13 @@ def run_ours(args) -> int:
                          "hbm_fraction_single_pass": per_gpu / (peaks["hbm_gbs"] * 1e9 / 0.25),
                          "hbm_fraction_k_pass": per_gpu / (peaks["hbm_gbs"] * 1e9 / 0.25 * k),
                          "hbm_of": peaks.get("source")},
-            "phase": {"halo_wait_us_per_gen": (phase["halo_wait_ns"][0] + phase["halo_wait_ns"][1]) * 1e-3
-                      / (2 * ncg) / max(1, gens_total),
+            "phase": {"halo_wait_us_per_gen": (phase["halo_wait_ns"][0] * 1e-3 / max(1, gens_total))
+                      if plan["mode_name"] == "resident" else
+                      (phase["halo_wait_ns"][0] + phase["halo_wait_ns"][1]) * 1e-3 / (2 * ncg) / max(1, gens_total),
                       "halo_waits": phase["halo_waits"],
                       "note": "rank 0: time edge warps spent spinning on a neighbour's halo flag, mean over the "
-                              "edge warps of both sides, per generation"},
+                              "edge warps of both sides, per generation (resident mode: time the CTA at the ring edge "
+                              "spent between pushing its rows and having both halos, per generation)"},
             "population_after_run": pop,
             "host_checks": len(checks),
         }

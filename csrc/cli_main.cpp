@@ -96,6 +96,7 @@ int main(int argc, char** argv) {
       else if (m == "fused") mode = GOL_MODE_FUSED;
       else if (m == "persistent") mode = GOL_MODE_PERSISTENT;
       else if (m == "tma") mode = GOL_MODE_TMA;
+      else if (m == "resident") mode = GOL_MODE_RESIDENT;
       else {
         fprintf(stderr, "gol: unknown mode %s\n", m.c_str());
         return 255;

@@ -1032,6 +1032,301 @@ __global__ void __launch_bounds__(MAXT, MINB) life_flow_kernel(SlabState* states
   }
 }
 
+// ---- N-K3b: resident kernel (small slabs) ---------------------------------------------------
+// A slab that fits in shared memory (4096^2 cells = 2 MiB over 148 SMs) is not bound by
+// throughput but by what happens between passes: a launch, or a release / acquire hand-off
+// through L2, costs more than the pass itself.  Here every CTA keeps its strip of rows in shared
+// memory for the WHOLE step: it is loaded once (cp.async.bulk, the TMA engine's 1-D copy) and
+// written back once.  One generation is one sweep over the shared-memory strip by all warps
+// (3-row register window per lane, x-neighbour words read from shared memory, so no halo lanes
+// and no shuffles) followed by a block barrier.  Every K generations neighbouring CTAs swap K
+// halo rows as flag-in-data words: straight into the neighbour's shared memory when it is in
+// the same thread-block cluster (mapa + st.shared::cluster, DSMEM), through a mailbox in L2
+// otherwise, and through the ring neighbour's ll_recv buffers at the two slab edges (NVLink).
+// The reader polls the words themselves; there is no flag, fence or cluster barrier per pass.
+// Replaces the whole loop of gol-main.c:94-116 for slabs of up to a few MiB.
+namespace resident {
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t cluster_map(uint32_t local_smem_addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_ll(uint32_t addr, uint64_t v, uint32_t seq) {
+  const unsigned long long a = (v & 0xffffffffull) | ((unsigned long long)seq << 32);
+  const unsigned long long b = (v >> 32) | ((unsigned long long)seq << 32);
+  asm volatile("st.shared::cluster.v2.u64 [%0], {%1, %2};" ::"r"(addr), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_shared_ll(uint32_t addr, unsigned long long& a, unsigned long long& b) {
+  asm volatile("ld.volatile.shared.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void ld_global_ll(const uint64_t* p, unsigned long long& a, unsigned long long& b) {
+  asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// cp.async.bulk global -> shared, completion on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_addr(src)), "r"(bytes)
+               : "memory");
+}
+}  // namespace resident
+
+namespace resident {
+enum { kRing = 0, kCluster = 1, kMail = 2 };   // how a strip boundary's halo rows travel
+
+// Where CTA `cta` of slab `sidx` receives the halo of side (0 = rows above, 1 = rows below), parity par.
+__device__ __forceinline__ uint64_t* mail_slot(const ResidentParams& rp, int sidx, int cta, int side, int par) {
+  return rp.mail + ((((int64_t)sidx * rp.ctas_per_slab + cta) * 2 + side) * 2 + par) * rp.mail_slot;
+}
+
+// One halo word, polled until both halves carry `seq` (flag-in-data); shared-memory or global slot.
+// The watchdog is looked at every 256 polls only: its clock read and the error-flag load cost more
+// than the poll itself.
+__device__ __forceinline__ uint64_t poll_word(SlabState* st, bool in_smem, const uint64_t* slot, int64_t idx,
+                                              uint32_t seq, int side) {
+  unsigned long long a, b, t0 = 0;
+  unsigned spins = 0;
+  if (!in_smem && !GOL_CHK(slot + idx * 2, 16)) return 0;
+  for (;;) {
+    if (in_smem) ld_shared_ll(smem_addr(slot + idx * 2), a, b);
+    else ld_global_ll(slot + idx * 2, a, b);
+    if ((uint32_t)(a >> 32) == seq && (uint32_t)(b >> 32) == seq) break;
+    if ((++spins & 255u) == 0) {
+      if (!t0) t0 = globaltimer_ns();
+      if (globaltimer_ns() - t0 > st->watchdog_ns || *(volatile int*)&st->error) {
+        atomicCAS(&st->error, 0, 1 + side);
+        break;
+      }
+    }
+  }
+  return (a & 0xffffffffull) | (b << 32);
+}
+
+// One generation of shared-memory rows [lo, hi) (row index = y - row_base) of the strip: words at
+// sm[cur + row * ws + w] -> sm[nxt + ...].  Warp (cb, rs) sweeps its share of the rows of column
+// block cb top to bottom; each lane keeps the horizontal sums of the two previous rows of its word in
+// registers and has the three words of the next row in flight while it computes the current one.
+// `sm` is the kernel's extern __shared__ array itself, so the accesses compile to LDS / STS.
+__device__ __forceinline__ void sweep(uint64_t* sm, int cur, int nxt, int lo, int hi, int ws, int warp, int nwarps,
+                                      int lane) {
+  const int ncb = (ws + 31) >> 5;
+  const int nrs = nwarps >= ncb ? nwarps / ncb : 1;          // warps that share a column block
+  const int rs = nwarps >= ncb ? warp / ncb : 0;
+  if (rs >= nrs) return;
+  const int n = hi - lo;
+  const int ya = lo + n * rs / nrs, yb = lo + n * (rs + 1) / nrs;
+  if (ya >= yb) return;
+  for (int cb = warp % ncb; cb < ncb; cb += (nwarps >= ncb ? ncb : nwarps)) {
+    const int w = cb * 32 + lane;
+    if (w >= ws) continue;
+    const int wl = w ? w - 1 : ws - 1, wr = w + 1 < ws ? w + 1 : 0;   // torus in x
+    Stage s;
+    s.lo.a0 = s.lo.a1 = s.lo.b0 = s.lo.b1 = s.lo.c = 0;
+    s.hi.a0 = s.hi.a1 = s.hi.b0 = s.hi.b1 = s.hi.c = 0;
+    // feed one row (its word c and the neighbouring words l, r); returns generation + 1 of the row before
+    auto feed = [&](uint64_t c, uint64_t l, uint64_t r) -> uint64_t {
+      const uint32_t clo = (uint32_t)c, chi = (uint32_t)(c >> 32);
+      // even columns (low half): left = previous odd column, right = odd column at the same index
+      const uint32_t Llo = __funnelshift_l((uint32_t)(l >> 32), chi, 1);
+      const uint32_t Rhi = __funnelshift_r(clo, (uint32_t)r, 1);
+      const uint32_t h0lo = lop3<0x96>(Llo, clo, chi), h1lo = lop3<0xE8>(Llo, clo, chi);
+      const uint32_t h0hi = lop3<0x96>(clo, chi, Rhi), h1hi = lop3<0xE8>(clo, chi, Rhi);
+      const uint32_t olo = stage_half(s.lo, h0lo, h1lo, clo);
+      const uint32_t ohi = stage_half(s.hi, h0hi, h1hi, chi);
+      return ((uint64_t)ohi << 32) | olo;
+    };
+    int pc = cur + (ya - 1) * ws + w, pl = cur + (ya - 1) * ws + wl, pr = cur + (ya - 1) * ws + wr;
+    int out = nxt + ya * ws + w;
+    // rows ya-1 and ya only fill the window; from row ya+1 on every row fed yields the row above it.
+    // The words of row y+1 are in flight while row y is computed; the last iteration reads one row
+    // past yb, which is still inside the kernel's shared memory (the other buffer or the landing zones).
+    uint64_t c0 = sm[pc], l0 = sm[pl], r0 = sm[pr];
+    pc += ws; pl += ws; pr += ws;
+    uint64_t c1 = sm[pc], l1 = sm[pl], r1 = sm[pr];
+    pc += ws; pl += ws; pr += ws;
+    feed(c0, l0, r0);
+    c0 = sm[pc]; l0 = sm[pl]; r0 = sm[pr];
+    pc += ws; pl += ws; pr += ws;
+    feed(c1, l1, r1);
+#pragma unroll 2
+    for (int y = ya + 1; y <= yb; ++y) {
+      c1 = sm[pc]; l1 = sm[pl]; r1 = sm[pr];
+      pc += ws; pl += ws; pr += ws;
+      sm[out] = feed(c0, l0, r0);
+      out += ws;
+      c0 = c1; l0 = l1; r0 = r1;
+    }
+  }
+}
+}  // namespace resident
+
+__global__ void __launch_bounds__(512, 1) life_resident_kernel(SlabState* states, ResidentParams rp) {
+  using namespace resident;
+  extern __shared__ __align__(16) uint64_t rsmem[];
+  __shared__ __align__(8) uint64_t load_bar;
+  const int tid = threadIdx.x, nthreads = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
+  const int C = rp.ctas_per_slab, K = rp.K;
+  const int sidx = blockIdx.x / C, cta = blockIdx.x - sidx * C;
+  SlabState* st = states + sidx;
+  const int64_t H = st->H, stride = st->stride;
+  const int ws = (int)st->ws;
+  const int64_t r0 = H * cta / C, r1 = H * (cta + 1) / C;        // my rows [r0, r1)
+  const int64_t row_base = r0 - K;                                // shared-memory row 0 <-> y = r0 - K
+  const int nr = (int)(r1 - r0);                                  // my row count
+  const int boff[2] = {0, rp.rows_alloc * ws};                    // word offsets of the two row buffers in rsmem
+  uint64_t* buf[2] = {rsmem, rsmem + (int64_t)rp.rows_alloc * ws};
+  uint64_t* land = rsmem + 2 * (int64_t)rp.rows_alloc * ws;       // [side][parity][K * ws * 2]: DSMEM landing zones
+  const int64_t land_slot = 2 * (int64_t)K * ws;
+  const int cs = rp.cluster, cr = cta % cs;
+  const int up_kind = cta == 0 ? kRing : (cr != 0 ? kCluster : kMail);
+  const int dn_kind = cta == C - 1 ? kRing : (cr != cs - 1 ? kCluster : kMail);
+
+  // landing zones start with exchange number 0 (never valid); nobody may write into them before
+  for (int64_t i = tid; i < 4 * land_slot; i += nthreads) land[i] = 0;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&load_bar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (cs > 1) cluster_sync_all();
+
+  // ---- load my strip (current generation) into buf[0]
+  const uint64_t* gin = st->buf[st->pass & 1] + (int64_t)st->G * stride;
+  const int64_t nrows = r1 - r0;
+  if (rp.use_bulk) {
+    // rows are contiguous (stride == ws): the TMA engine copies the strip in chunks of <= 64 KiB
+    if (tid == 0) {
+      const uint64_t total = (uint64_t)nrows * ws * 8;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&load_bar)),
+                   "r"((uint32_t)total)
+                   : "memory");
+      for (uint64_t off = 0; off < total; off += 65536) {
+        const uint32_t n = (uint32_t)(total - off < 65536 ? total - off : 65536);
+        if (GOL_CHK((const char*)(gin + r0 * stride) + off, n))
+          bulk_g2s((char*)(buf[0] + (int64_t)K * ws) + off, (const char*)(gin + r0 * stride) + off, n, &load_bar);
+      }
+    }
+    uint32_t done = 0;
+    while (!done)
+      asm volatile(
+          "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(smem_addr(&load_bar))
+          : "memory");
+  } else {
+    for (int64_t i = tid; i < nrows * ws; i += nthreads) {
+      const int64_t r = i / ws, w = i - r * ws;
+      buf[0][(K + r) * ws + w] = ld_cg(gin + (r0 + r) * stride + w);
+    }
+  }
+  __syncthreads();
+
+  const unsigned long long exch0 = st->exch;
+  unsigned long long wait_acc = 0;   // thread 0: time between "my rows are pushed" and "my halos are in"
+  int cb = 0;
+  for (int p = 0; p < rp.npasses; ++p) {
+    const int kk = p == rp.npasses - 1 ? rp.last_k : K;
+    const unsigned long long e = exch0 + (unsigned long long)p;
+    const uint32_t seq = (uint32_t)(e + 1ull);
+    const int par = (int)(e & 1ull);
+    const uint64_t* cur = buf[cb];
+
+    // ---- push my K top rows to the strip above (its bottom halo) and my K bottom rows to the strip below
+    for (int i = tid; i < 2 * K * ws; i += nthreads) {
+      const int side = i >= K * ws;                          // 0: my top rows go up, 1: my bottom rows go down
+      const int j = side ? i - K * ws : i;
+      const int r = j / ws, w = j - r * ws;
+      const int64_t y = side ? r1 - K + r : r0 + r;
+      const uint64_t v = cur[(y - row_base) * ws + w];
+      const int kind = side ? dn_kind : up_kind;
+      if (kind == kRing) {
+        ll_store(st->peer_ll[side][par] + (r * stride + w) * 2, v, seq);
+      } else if (kind == kCluster) {
+        // the neighbour's landing zone for its opposite side, same offset inside its shared memory
+        const uint32_t mine = smem_addr(land + ((1 - side) * 2 + par) * land_slot + (r * ws + w) * 2);
+        st_cluster_ll(cluster_map(mine, (uint32_t)(side ? cr + 1 : cr - 1)), v, seq);
+      } else {
+        ll_store(mail_slot(rp, sidx, side ? cta + 1 : cta - 1, 1 - side, par) + (r * ws + w) * 2, v, seq);
+      }
+    }
+    // ---- receive the K rows above and below into the halo rows of the current buffer
+    const unsigned long long tw0 = tid == 0 ? globaltimer_ns() : 0ull;
+    uint64_t* curw = buf[cb];
+    for (int i = tid; i < 2 * K * ws; i += nthreads) {
+      const int side = i >= K * ws;
+      const int j = side ? i - K * ws : i;
+      const int r = j / ws, w = j - r * ws;
+      const int kind = side ? dn_kind : up_kind;
+      uint64_t v;
+      if (kind == kRing) v = poll_word(st, false, st->ll_recv[side][par], r * stride + w, seq, side);
+      else if (kind == kCluster) v = poll_word(st, true, land + (side * 2 + par) * land_slot, r * ws + w, seq, side);
+      else v = poll_word(st, false, mail_slot(rp, sidx, cta, side, par), r * ws + w, seq, side);
+      const int64_t y = side ? r1 + r : r0 - K + r;
+      curw[(y - row_base) * ws + w] = v;
+    }
+    __syncthreads();
+    if (tid == 0) wait_acc += globaltimer_ns() - tw0;   // push is done, everything from here to the barrier is waiting
+
+    // ---- kk generations on a shrinking window: after generation g rows [r0-(kk-1-g), r1+(kk-1-g)) are valid
+    for (int g = 0; g < kk; ++g) {
+      const int m = kk - 1 - g;
+      sweep(rsmem, boff[cb], boff[cb ^ 1], K - m, K + nr + m, ws, warp, nwarps, lane);
+      __syncthreads();
+      cb ^= 1;
+    }
+  }
+
+  // ---- write my strip back (next buffer of the slab)
+  uint64_t* gout = st->buf[(st->pass + 1) & 1] + (int64_t)st->G * stride;
+  if (rp.use_bulk) {
+    if (tid == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> async proxy reads
+      const uint64_t total = (uint64_t)nrows * ws * 8;
+      for (uint64_t off = 0; off < total; off += 65536) {
+        const uint32_t n = (uint32_t)(total - off < 65536 ? total - off : 65536);
+        if (GOL_CHK((char*)(gout + r0 * stride) + off, n))
+          bulk_s2g((char*)(gout + r0 * stride) + off, (const char*)(buf[cb] + (int64_t)K * ws) + off, n);
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+  } else {
+    for (int64_t i = tid; i < nrows * ws; i += nthreads) {
+      const int64_t r = i / ws, w = i - r * ws;
+      st_cg(gout + (r0 + r) * stride + w, buf[cb][(K + r) * ws + w]);
+    }
+  }
+  __syncthreads();
+  if (cs > 1) cluster_sync_all();   // nobody leaves while a cluster neighbour may still write into its shared memory
+
+  // the last CTA of the launch advances the slab counters (one buffer flip per launch)
+  if (tid == 0) {
+    atomicAdd(&st->wait_ns[cta == 0 ? 0 : 1], wait_acc);   // [0]: the CTA at the ring edge, [1]: all the others
+    atomicAdd(&st->wait_count[cta == 0 ? 0 : 1], (unsigned long long)rp.npasses);
+    __threadfence();
+    if (atomicAdd(&rp.ctl[1], 1u) == gridDim.x - 1) {
+      __threadfence();
+      for (int s2 = 0; s2 < rp.nslabs; ++s2) {
+        states[s2].pass += 1ull;
+        states[s2].exch += (unsigned long long)rp.npasses;
+      }
+      rp.ctl[1] = 0u;
+      __threadfence();
+    }
+  }
+}
+
+
 // ---- N-K4: pattern initialisers ------------------------------------------------
 __global__ void pattern_init_kernel(uint64_t* rows, int64_t stride, PatternArgs a) {
   const int64_t ws = words_per_row(a.W);
@@ -1506,6 +1801,76 @@ cudaError_t launch_flow(int K, SlabState* d_states, const FlowParams& fp0, int t
 
 // Grid of a grid-stride helper kernel: enough blocks for the data, at most 32 per SM of the
 // current device.
+// ---- resident kernel: launch with a cluster dimension, all CTAs co-resident (cooperative) ---------
+static cudaError_t resident_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int nctas, int threads,
+                                   size_t smem, int cluster, cudaStream_t s) {
+  cudaError_t e = cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem);
+  if (e != cudaSuccess) return e;
+  *cfg = cudaLaunchConfig_t{};
+  cfg->gridDim = dim3((unsigned)nctas);
+  cfg->blockDim = dim3((unsigned)threads);
+  cfg->dynamicSmemBytes = smem;
+  cfg->stream = s;
+  int n = 0;
+  attr[n].id = cudaLaunchAttributeCooperative;   // CTAs poll each other's halo words: all must be resident
+  attr[n].val.cooperative = 1;
+  ++n;
+  if (cluster > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = (unsigned)cluster;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg->attrs = attr;
+  cfg->numAttrs = (unsigned)n;
+  return cudaSuccess;
+}
+
+size_t resident_smem_bytes(int rows_alloc, int64_t ws, int K) {
+  return ((size_t)2 * (size_t)rows_alloc * (size_t)ws + (size_t)8 * (size_t)K * (size_t)ws) * 8;
+}
+
+// CTAs of `threads` threads and `smem` bytes that can be resident at once in clusters of `cluster`.
+int resident_max_ctas(int threads, size_t smem, int cluster, int device) {
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  if (cluster <= 1) {
+    int nb = 0;
+    if (cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)life_resident_kernel, threads, smem) != cudaSuccess) {
+      cudaGetLastError();
+      return 0;
+    }
+    return nb > 0 ? sms : 0;   // one CTA per SM by design (__launch_bounds__(512, 1))
+  }
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+  if (resident_config(&cfg, attr, sms / cluster * cluster, threads, smem, cluster, nullptr) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int nclusters = 0;
+  if (cudaOccupancyMaxActiveClusters(&nclusters, (const void*)life_resident_kernel, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return nclusters * cluster;
+}
+
+cudaError_t launch_resident(SlabState* d_states, const ResidentParams& rp0, int threads, size_t smem, cudaStream_t s) {
+  cudaLaunchConfig_t cfg;
+  cudaLaunchAttribute attr[2];
+  ResidentParams rp = rp0;
+  cudaError_t e = resident_config(&cfg, attr, rp.nslabs * rp.ctas_per_slab, threads, smem, rp.cluster, s);
+  if (e != cudaSuccess) return e;
+  void* args[] = {(void*)&d_states, (void*)&rp};
+  count_launch(1);
+  return cudaLaunchKernelExC(&cfg, (const void*)life_resident_kernel, args);
+}
+
 static int grid_for(int64_t total, int threads) {
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||

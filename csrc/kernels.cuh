@@ -51,6 +51,12 @@ cudaError_t launch_prime(SlabState* d_states, int nslabs, int depth, int64_t max
 cudaError_t launch_flow(int K, SlabState* d_states, const FlowParams& fp, int threads, int nctas,
                         cudaStream_t s);
 
+// Resident kernel (small slabs, strips kept in shared memory, thread-block clusters; ResidentParams in
+// internal.h).  smem = resident_smem_bytes(...); resident_max_ctas = CTAs that can be co-resident.
+size_t resident_smem_bytes(int rows_alloc, int64_t ws, int K);
+int resident_max_ctas(int threads, size_t smem, int cluster, int device);
+cudaError_t launch_resident(SlabState* d_states, const ResidentParams& rp, int threads, size_t smem, cudaStream_t s);
+
 cudaError_t launch_pattern_init(uint64_t* d_rows, int64_t stride, const PatternArgs& a,
                                 cudaStream_t s);
 cudaError_t launch_pack(const uint8_t* d_cells, uint64_t* d_words, int64_t W, int64_t H,

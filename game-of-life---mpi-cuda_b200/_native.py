@@ -21,7 +21,7 @@ _LIB_PATH = os.path.join(_HERE, "_lib", "libgol_b200_debug.so" if os.environ.get
                          else "libgol_b200.so")
 
 BACKEND_CPU, BACKEND_CUDA = 0, 1
-MODES = {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4}
+MODES = {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4, "resident": 5}
 MODE_NAMES = {v: k for k, v in MODES.items()}
 FLAG_NO_GRAPH, FLAG_NO_PEER_ACCESS, FLAG_CPU_SCHEDULE = 1, 2, 4
 EXPORT_BYTES = 256

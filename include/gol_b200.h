@@ -40,6 +40,9 @@ extern "C" {
 #define GOL_MODE_PERSISTENT 3  /* one launch for the whole step(): persistent warps,
                                   per-strip dependencies instead of grid barriers */
 #define GOL_MODE_TMA 4         /* fused, input rows fed by TMA bulk copies      */
+#define GOL_MODE_RESIDENT 5    /* small slabs: strips stay in shared memory for the whole
+                                  step(), one CTA per strip, thread-block clusters,
+                                  halo rows between CTAs over DSMEM / L2 mailboxes    */
 
 #define GOL_MAX_GHOST 32       /* deepest exchange (rows per side)              */
 

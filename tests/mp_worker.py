@@ -28,6 +28,8 @@ def main() -> int:
         ("fused", 1, 1, 256, 64, 19, 4),
         ("tma", 4, 4, 10240, 256, 29, 6),
         ("persistent", 4, 4, 2048, 256, 43, 6),
+        ("resident", 4, 4, 4096, 512, 43, 6),
+        ("resident", 3, 3, 2048, 200, 20, 5),
         ("persistent", 2, 8, 1024, 128, 40, 5),
         ("generic", 0, 0, 200, 33, 9, 6),
         ("auto", 0, 0, 256, 256, 24, 5),

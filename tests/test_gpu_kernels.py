@@ -302,3 +302,19 @@ def test_flag_in_data_halo_protocol(monkeypatch, mode, k, depth, R):
     got, plan = run_gpu(6, W, H, R, gens, mode=mode, k=k, depth=depth, seed=41, chunks=[depth + 1, gens - depth - 1])
     assert plan["mode_name"] == mode
     assert (got == expected(6, W, H, R, gens, seed=41)).all()
+
+
+# ------------------------------------------------------------------ resident kernel (N-K3b)
+def test_auto_picks_the_resident_kernel_for_small_tall_slabs():
+    got, plan = run_gpu(6, 4096, 1024, 2, 19, seed=3, chunks=[7, 12])
+    assert plan["mode_name"] == "resident" and plan["temporal_k"] == 4
+    assert (got == expected(6, 4096, 1024, 2, 19, seed=3)).all()
+    _, plan = run_gpu(6, 4096, 512, 1, 1)          # too short to give every SM a strip: stays fused
+    assert plan["mode_name"] == "fused"
+
+
+@pytest.mark.parametrize("pattern", [1, 2, 3, 4, 5])
+def test_resident_reference_patterns(pattern):
+    got, plan = run_gpu(pattern, 256, 256, 2, 24, mode="resident", k=4)
+    assert plan["mode_name"] == "resident"
+    assert (got == expected(pattern, 256, 256, 2, 24)).all()

@@ -59,3 +59,31 @@ def test_persistent_many_strips_and_passes():
     # tall enough for hundreds of interior strips per pass and tens of passes in flight
     run("persistent", 8192, 2048, 1, gens=83, seed=5)
     run("persistent", 2048, 1500, 3, gens=61, k=2, depth=2, seed=6)
+
+
+# ------------------------------------------------------------------ resident kernel (clusters / DSMEM)
+@pytest.mark.parametrize("W,H,R", [(4096, 512, 1), (4096, 300, 2), (2048, 257, 3), (8192, 96, 1), (64, 40, 2),
+                                   (1984, 130, 2)])
+@pytest.mark.parametrize("K", [1, 4, 5])
+def test_resident_kernel_vs_numpy(W, H, R, K):
+    """Strips stay in shared memory for the whole step; halo rows travel as flag-in-data words over
+    DSMEM inside a cluster, L2 mailboxes between clusters and ll_recv buffers between ranks."""
+    gens = 3 * K + 2                     # the last pass is a partial one
+    run("resident", W, H, R, gens=gens, k=K, seed=W + H + K, chunks=[K + 1, gens - K - 1])
+
+
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
+@pytest.mark.parametrize("bulk", [True, False])
+def test_resident_cluster_sizes_and_copy_paths(monkeypatch, cluster, bulk):
+    monkeypatch.setenv("GOL_RESIDENT_CLUSTER", str(cluster))
+    if not bulk:
+        monkeypatch.setenv("GOL_RESIDENT_NO_BULK", "1")
+    run("resident", 4096, 1024, 1, gens=37, k=4, seed=cluster)
+    run("resident", 2048, 640, 2, gens=21, k=2, seed=cluster + 10)
+
+
+def test_resident_rejects_slabs_that_do_not_fit():
+    from gol_b200 import GolError
+
+    with pytest.raises(GolError, match="resident"):
+        World(65536, 16384, backend="cuda", mode="resident")

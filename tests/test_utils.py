@@ -29,5 +29,5 @@ def test_package_surface():
     assert gol_b200.version().startswith("gol_b200")
     for name in ("Life", "World", "GolError", "PATTERNS", "pattern_bytes", "launch_count"):
         assert hasattr(gol_b200, name)
-    assert gol_b200._native.MODES == {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4}
+    assert gol_b200._native.MODES == {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4, "resident": 5}
     assert gol_b200.launch_count() >= 0
