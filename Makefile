@@ -17,7 +17,7 @@ HDRS      := $(wildcard csrc/*.h csrc/*.cuh include/*.h)
 DBGLIB    := $(PKG)/_lib/libgol_b200_debug.so
 DBGOBJS   := $(patsubst csrc/%.cu,$(OBJDIR)/debug/%.o,$(CU_SRCS)) $(patsubst csrc/%.cpp,$(OBJDIR)/debug/%.o,$(CXX_SRCS))
 
-all: $(LIB) $(BIN) $(DBGLIB)
+all: $(LIB) $(BIN) $(DBGLIB) bin/microbench_sync
 
 # bounds-checking build: same sources with -DGOL_DEBUG_BOUNDS=1 (include/gol_b200.h, "Memory-safety build")
 $(OBJDIR)/debug/%.o: csrc/%.cu $(HDRS)
@@ -50,9 +50,16 @@ $(BIN): csrc/cli_main.cpp $(LIB) $(HDRS)
 	@mkdir -p bin
 	g++ -O2 -std=c++17 -Wall -o $@ csrc/cli_main.cpp -L$(PKG)/_lib -lgol_b200 -Wl,-rpath,'$$ORIGIN/../$(PKG)/_lib' -lpthread
 
+# per-kernel SASS listings under profiles/sass/ (no GPU needed)
 sass: $(LIB)
-	@mkdir -p profiles/sass
-	cuobjdump -sass $(LIB) > profiles/sass/libgol_b200.sass
+	python scripts/split_sass.py
+
+# hand-off latencies between CTAs (cluster barrier, DSMEM, L2): run on a GPU box
+bin/microbench_sync: scripts/microbench_sync.cu
+	@mkdir -p bin
+	$(NVCC) $(ARCH) -O3 -o $@ $<
+
+microbench: bin/microbench_sync
 
 test: all
 	python -m pytest tests -q -m "not gpu"
@@ -63,4 +70,4 @@ test-gpu: all
 clean:
 	rm -rf $(OBJDIR) $(LIB) $(DBGLIB) $(BIN)
 
-.PHONY: all clean sass test test-gpu debug
+.PHONY: all clean sass test test-gpu debug microbench

@@ -298,7 +298,7 @@ def run_ours(args) -> int:
 
     # ---- correctness gate on the very path that is timed below (same mode, k, depth, ring wiring):
     # a small torus through Life -> compared with an independent numpy stepper
-    vW, vH, vG = 2048, 256, 37
+    vW, vH, vG = (10240 if args.mode == "tma" else 2048), 256, 37   # mode tma needs >= 144 words per row
     vlife = Life(vW, vH, mode=args.mode, k=args.k, depth=args.depth, threads=args.threads, distributed=distributed)
     vlife.init(6, seed=99, density=0.5)
     vlife.step(20).step(vG - 20).sync()

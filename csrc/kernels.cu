@@ -1807,6 +1807,10 @@ static cudaError_t resident_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute*
   cudaError_t e = cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem);
   if (e != cudaSuccess) return e;
+  // all of the SM's L1 / shared memory as shared memory: the kernel lives in it
+  cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                       cudaSharedmemCarveoutMaxShared);
+  cudaGetLastError();
   *cfg = cudaLaunchConfig_t{};
   cfg->gridDim = dim3((unsigned)nctas);
   cfg->blockDim = dim3((unsigned)threads);
@@ -1838,6 +1842,8 @@ int resident_max_ctas(int threads, size_t smem, int cluster, int device) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (cluster <= 1) {
     int nb = 0;
+    cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                         cudaSharedmemCarveoutMaxShared);
     if (cudaFuncSetAttribute((const void*)life_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess ||
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, (const void*)life_resident_kernel, threads, smem) != cudaSuccess) {

@@ -257,10 +257,11 @@ int make_plan(gol_world* w) {
       while (depth > w->H && depth > 1) depth /= 2;
       if (K > depth) K = largest_k_le(depth);
       mode = GOL_MODE_FUSED;
-      // Small slabs (<= 4 MiB packed, tall enough to give every SM a strip) are bound by the
+      // Small slabs (<= 8 MiB packed, tall enough to give every SM a strip) are bound by the
       // hand-off between passes, not by throughput: the shared-memory resident kernel steps a
-      // 4096^2 slab 1.8x faster than the graph of fused passes (5.45 vs 9.7 ms per 4096 generations).
-      if (w->cuda && !w->auto_no_resident && w->H >= 1024 && w->H * w->ws * 8 <= (4ll << 20) &&
+      // 4096^2 slab in 4.9 instead of 8.5 ms per 4096 generations and an 8192^2 slab at 25 instead
+      // of 16.6 TCUPS (profiles/r2/).  A slab whose strips do not fit shared memory falls back.
+      if (w->cuda && !w->auto_no_resident && w->H >= 1024 && w->H * w->ws * 8 <= (8ll << 20) &&
           (c.exchange_depth <= 0 || c.exchange_depth == K))
         mode = GOL_MODE_RESIDENT;
     } else {
@@ -344,28 +345,48 @@ int finish_plan_resident(gol_world* w) {
   const int K = p.temporal_k;
   int forced = 0;
   if (const char* e = getenv("GOL_RESIDENT_CLUSTER")) forced = atoi(e);
+  // Cluster size: pairs by default.  148 SMs pack perfectly into clusters of 2, and the DSMEM
+  // hand-off inside a pair is a little faster than the L2 mailbox (5.34 vs 5.43 ms per 4096
+  // generations at 4096^2).  Clusters of 4 and 8 cannot cover every SM of the 16 / 18 / 20-SM GPCs
+  // with one CTA each, so some SMs host two strips and the step takes 8 ms: GOL_RESIDENT_CLUSTER
+  // selects them for experiments only.
   int best_c = 0, best_cs = 1;
+  size_t smem = 0;
+  int rows = 0;
   for (int cs : {8, 4, 2, 1}) {
-    if (forced > 0 && cs != forced) continue;
+    if (forced > 0 ? cs != forced : cs > 2) continue;
     // one CTA per SM: a second resident CTA would halve the strips and double the halo rows recomputed
     const int cap = std::min(resident_max_ctas(p.threads_per_block, 64 * 1024, cs, dev), w->sms / cs * cs);
     int64_t c = std::min<int64_t>(cap / (int64_t)slabs_per_dev, w->H / K);   // every strip holds at least K rows
     if (w->cfg.reserved > 0) c = std::min<int64_t>(c, (w->H + w->cfg.reserved - 1) / w->cfg.reserved);
     c = c / cs * cs;
+    if (c < 1) continue;
+    // the launch is cooperative: check co-residency with the shared memory the strips really need
+    const int r = (int)((w->H + c - 1) / c);
+    const size_t sm = resident_smem_bytes(r + 2 * K, w->ws, K);
+    if (sm + 1024 > (size_t)max_smem) {
+      if (best_c == 0) {
+        rows = r;
+        smem = sm;
+      }
+      continue;
+    }
+    if (resident_max_ctas(p.threads_per_block, sm, cs, dev) < c * (int64_t)slabs_per_dev) continue;
     if (c > best_c) {   // larger clusters are tried first and kept on ties
       best_c = (int)c;
       best_cs = cs;
+      rows = r;
+      smem = sm;
     }
   }
-  if (best_c < 1)
+  if (best_c < 1) {
+    if (smem)
+      return set_error(GOL_ERR_UNSUPPORTED,
+                       "mode resident keeps %d rows x %lld words per CTA in shared memory (%zu bytes, limit %d): the slab "
+                       "is too large, use mode fused or persistent", rows + 2 * K, (long long)w->ws, smem, max_smem);
     return set_error(GOL_ERR_UNSUPPORTED, "mode resident: no co-resident launch shape for %zu slab(s) per device",
                      slabs_per_dev);
-  const int rows = (int)((w->H + best_c - 1) / best_c);
-  const size_t smem = resident_smem_bytes(rows + 2 * K, w->ws, K);
-  if (smem + 1024 > (size_t)max_smem)
-    return set_error(GOL_ERR_UNSUPPORTED,
-                     "mode resident keeps %d rows x %lld words per CTA in shared memory (%zu bytes, limit %d): the slab "
-                     "is too large, use mode fused or persistent", rows + 2 * K, (long long)w->ws, smem, max_smem);
+  }
   p.strip_rows = rows;
   p.ctas_per_slab = best_c;
   p.regs_hint = best_cs;   // cluster size

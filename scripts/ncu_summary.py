@@ -42,7 +42,55 @@ def run(args):
     return subprocess.run(["ncu", "-i"] + args, capture_output=True, text=True).stdout
 
 
+TABLE = [
+    ("gpu__time_duration.sum", "duration"),
+    ("launch__grid_size", "grid"),
+    ("launch__block_size", "block"),
+    ("launch__registers_per_thread", "regs"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "occupancy %"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "SM %"),
+    ("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "ALU %"),
+    ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "LSU %"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM %"),
+    ("dram__bytes_read.sum", "DRAM read"),
+    ("dram__bytes_write.sum", "DRAM written"),
+    ("lts__t_sector_hit_rate.pct", "L2 hit %"),
+]
+
+
+def table_of_all(rep, title):
+    """--all: one row per distinct kernel of the report (first launch of each)."""
+    raw = list(csv.reader(io.StringIO(run([rep, "--page", "raw", "--csv"]))))
+    hdr, units = raw[0], raw[1]
+    print(f"# {title}\n")
+    print(f"Source: `{rep.split('/')[-1]}` (ncu --set full --clock-control none), B200, one GPU; first launch of each kernel.\n")
+    print("| kernel | " + " | ".join(l for _, l in TABLE) + " |")
+    print("|---|" + "---|" * len(TABLE))
+    seen = set()
+    ik = hdr.index("Kernel Name")
+    for row in raw[2:]:
+        name = row[ik].split("(")[0].split("::")[-1]
+        if name in seen:
+            continue
+        seen.add(name)
+        cells = []
+        for key, _ in TABLE:
+            if key in hdr:
+                i = hdr.index(key)
+                v = row[i]
+                try:
+                    v = f"{float(v):.4g}"
+                except ValueError:
+                    pass
+                cells.append(f"{v} {units[i]}".strip())
+            else:
+                cells.append("-")
+        print(f"| `{name}` | " + " | ".join(cells) + " |")
+
+
 def main():
+    if len(sys.argv) > 3 and sys.argv[3] == "--all":
+        return table_of_all(sys.argv[1], sys.argv[2])
     rep, title = sys.argv[1], sys.argv[2]
     raw = list(csv.reader(io.StringIO(run([rep, "--page", "raw", "--csv"]))))
     hdr, units = raw[0], raw[1]
