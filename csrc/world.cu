@@ -1982,41 +1982,65 @@ int gol_world_dump_text(gol_world_t* w, int li, const char* dir) {
   Group& g = w->groups[(size_t)s.group];
   CU_TRY(cudaSetDevice(s.device));
   const int64_t pitch = (int64_t)align_up((size_t)(kTextCellOff + 2 * w->W + 1), 16);
-  int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(64ll << 20) / pitch);
+  // two slots of 32 MiB: chunk i+1 is formatted on the device and copied to the host while chunk i
+  // is written to the file
+  int64_t chunk_rows = std::max<int64_t>(1, (int64_t)(32ll << 20) / pitch);
   chunk_rows = std::min(chunk_rows, w->H);
-  char* d_text = nullptr;
-  char* h_text = nullptr;
-  CU_TRY(cudaMalloc((void**)&d_text, (size_t)(chunk_rows * pitch)));
-  debug_bounds_register(d_text, (size_t)(chunk_rows * pitch));
-  struct Unreg { char* p; ~Unreg() { debug_bounds_unregister(p); } } unreg{d_text};
-  cudaError_t e = cudaMallocHost((void**)&h_text, (size_t)(chunk_rows * pitch));
-  if (e != cudaSuccess) {
-    cudaFree(d_text);
-    return set_error(GOL_ERR_CUDA, "pinned allocation failed: %s", cudaGetErrorString(e));
+  const size_t slot_bytes = (size_t)(chunk_rows * pitch);
+  char* d_text[2] = {nullptr, nullptr};
+  char* h_text[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  FILE* fp = nullptr;
+  auto cleanup = [&]() {
+    for (int k = 0; k < 2; ++k) {
+      if (d_text[k]) {
+        debug_bounds_unregister(d_text[k]);
+        cudaFree(d_text[k]);
+      }
+      if (h_text[k]) cudaFreeHost(h_text[k]);
+      if (ev[k]) cudaEventDestroy(ev[k]);
+    }
+  };
+  cudaError_t e = cudaSuccess;
+  for (int k = 0; k < 2 && e == cudaSuccess; ++k) {
+    e = cudaMalloc((void**)&d_text[k], slot_bytes);
+    if (e == cudaSuccess) debug_bounds_register(d_text[k], slot_bytes);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&h_text[k], slot_bytes);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
   }
-  FILE* fp = fopen(path.c_str(), "w");
+  if (e != cudaSuccess) {
+    cleanup();
+    return set_error(GOL_ERR_CUDA, "text staging allocation failed: %s", cudaGetErrorString(e));
+  }
+  fp = fopen(path.c_str(), "w");
   if (!fp) {
-    cudaFree(d_text);
-    cudaFreeHost(h_text);
+    cleanup();
     return set_error(GOL_ERR_IO, "cannot open %s: %s", path.c_str(), strerror(errno));
   }
   rc = write_rank_header(fp, s.rank);
   const uint64_t* rows = cur_interior(w, s);
-  for (int64_t y0 = 0; y0 < w->H && rc == GOL_OK; y0 += chunk_rows) {
-    const int64_t n = std::min(chunk_rows, w->H - y0);
+  const int64_t nchunks = (w->H + chunk_rows - 1) / chunk_rows;
+  auto issue = [&](int64_t c) -> cudaError_t {
+    const int k = (int)(c & 1);
+    const int64_t y0 = c * chunk_rows, n = std::min(chunk_rows, w->H - y0);
+    cudaError_t ee = launch_format_rows(rows + y0 * w->stride, w->stride, w->W, n, w->H * s.rank + y0, d_text[k], pitch,
+                                        g.stream);
+    if (ee == cudaSuccess)
+      ee = cudaMemcpyAsync(h_text[k], d_text[k], (size_t)(n * pitch), cudaMemcpyDeviceToHost, g.stream);
+    if (ee == cudaSuccess) ee = cudaEventRecord(ev[k], g.stream);
+    return ee;
+  };
+  e = issue(0);
+  for (int64_t c = 0; c < nchunks && rc == GOL_OK && e == cudaSuccess; ++c) {
+    if (c + 1 < nchunks) e = issue(c + 1);   // its slot was written out two chunks ago
+    if (e == cudaSuccess) e = cudaEventSynchronize(ev[c & 1]);
+    if (e != cudaSuccess) break;
+    const int64_t y0 = c * chunk_rows, n = std::min(chunk_rows, w->H - y0);
     const int64_t first_global = w->H * s.rank + y0;
-    e = launch_format_rows(rows + y0 * w->stride, w->stride, w->W, n, first_global, d_text, pitch, g.stream);
-    if (e == cudaSuccess)
-      e = cudaMemcpyAsync(h_text, d_text, (size_t)(n * pitch), cudaMemcpyDeviceToHost, g.stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
-    if (e != cudaSuccess) {
-      rc = set_error(GOL_ERR_CUDA, "format_rows: %s", cudaGetErrorString(e));
-      break;
-    }
     for (int64_t r = 0; r < n; ++r) {
       char pre[40];
       const int plen = snprintf(pre, sizeof pre, "Row %2d: ", (int)(first_global + r));
-      const char* start = h_text + r * pitch + kTextCellOff - plen;
+      const char* start = h_text[c & 1] + r * pitch + kTextCellOff - plen;
       const size_t len = (size_t)plen + (size_t)(2 * w->W) + 1;
       if (fwrite(start, 1, len, fp) != len) {
         rc = set_error(GOL_ERR_IO, "short write to %s", path.c_str());
@@ -2024,9 +2048,10 @@ int gol_world_dump_text(gol_world_t* w, int li, const char* dir) {
       }
     }
   }
+  if (e != cudaSuccess) rc = set_error(GOL_ERR_CUDA, "format_rows: %s", cudaGetErrorString(e));
+  cudaStreamSynchronize(g.stream);
   if (fclose(fp) != 0 && rc == GOL_OK) rc = set_error(GOL_ERR_IO, "close of %s failed", path.c_str());
-  cudaFree(d_text);
-  cudaFreeHost(h_text);
+  cleanup();
   return rc;
 }
 
