@@ -67,9 +67,12 @@ def run_reference(args) -> int:
     rank, world, _ = env_rank()
     if world > 1:
         # launched under torchrun like our arm: rank 0 drives the reference's own launcher
+        import datetime
+
         import torch.distributed as dist
 
-        dist.init_process_group("gloo")
+        # the other ranks only wait for rank 0: the reference run may take a quarter of an hour
+        dist.init_process_group("gloo", timeout=datetime.timedelta(hours=3))
     out = {"impl": "reference"}
     if rank == 0:
         out = reference_measure(args)
