@@ -185,6 +185,7 @@ struct ResidentParams {
   int32_t nslabs, ctas_per_slab, cluster;
   int32_t rows_alloc;      // shared-memory rows per buffer: max strip rows + 2K
   int32_t use_bulk;        // strips are loaded / stored with cp.async.bulk (rows are contiguous: stride == ws)
+  int32_t smem_words;      // 64-bit words of dynamic shared memory (bounds-checking build: every offset is checked)
   uint64_t* mail;          // CTA-to-CTA halo mailboxes in global memory (flag-in-data words)
   int64_t mail_slot;       // words per (cta, side, parity) slot = 2 * K * ws
   unsigned int* ctl;       // [1]: CTAs finished (the last one advances the slab counters)

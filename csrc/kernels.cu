@@ -59,8 +59,19 @@ __device__ __noinline__ bool dbg_ok(const void* p, long long bytes, int line) {
   return false;
 }
 #define GOL_CHK(p, n) dbg_ok((const void*)(p), (long long)(n), __LINE__)
+// shared-memory word offset `off` (n words) inside a dynamic shared-memory array of `limit` words
+__device__ __noinline__ bool dbg_smem_bad(long long off, int line) {
+  if (atomicAdd(&g_dbg.violations, 1ull) == 0ull) {
+    g_dbg.first_bad = 0x5ed0000000000000ull | (unsigned long long)(off & 0xffffffffll);   // tag: shared-memory offset
+    g_dbg.first_line = line;
+  }
+  return false;
+}
+#define GOL_SCHK(off, n, limit) \
+  (((long long)(off) >= 0 && (long long)(off) + (long long)(n) <= (long long)(limit)) ? true : dbg_smem_bad((long long)(off), __LINE__))
 #else
 #define GOL_CHK(p, n) (true)
+#define GOL_SCHK(off, n, limit) (true)
 #endif
 
 constexpr unsigned kFull = 0xffffffffu;
@@ -1117,7 +1128,7 @@ __device__ __forceinline__ uint64_t poll_word(SlabState* st, bool in_smem, const
 // registers and has the three words of the next row in flight while it computes the current one.
 // `sm` is the kernel's extern __shared__ array itself, so the accesses compile to LDS / STS.
 __device__ __forceinline__ void sweep(uint64_t* sm, int cur, int nxt, int lo, int hi, int ws, int warp, int nwarps,
-                                      int lane) {
+                                      int lane, int limit) {
   const int ncb = (ws + 31) >> 5;
   const int nrs = nwarps >= ncb ? nwarps / ncb : 1;          // warps that share a column block
   const int rs = nwarps >= ncb ? warp / ncb : 0;
@@ -1146,6 +1157,11 @@ __device__ __forceinline__ void sweep(uint64_t* sm, int cur, int nxt, int lo, in
     };
     int pc = cur + (ya - 1) * ws + w, pl = cur + (ya - 1) * ws + wl, pr = cur + (ya - 1) * ws + wr;
     int out = nxt + ya * ws + w;
+    // bounds-checking build: the first and the last word this sweep touches (rows ya-1 .. yb+1 read,
+    // rows ya .. yb-1 written) must lie inside the kernel's shared memory
+    if (!GOL_SCHK(cur + (ya - 1) * ws, 1, limit) || !GOL_SCHK(cur + (yb + 1) * ws + ws - 1, 1, limit) ||
+        !GOL_SCHK(out, 1, limit) || !GOL_SCHK(nxt + (yb - 1) * ws + w, 1, limit))
+      continue;
     // rows ya-1 and ya only fill the window; from row ya+1 on every row fed yields the row above it.
     // The words of row y+1 are in flight while row y is computed; the last iteration reads one row
     // past yb, which is still inside the kernel's shared memory (the other buffer or the landing zones).
@@ -1247,14 +1263,17 @@ __global__ void __launch_bounds__(512, 1) life_resident_kernel(SlabState* states
       const int j = side ? i - K * ws : i;
       const int r = j / ws, w = j - r * ws;
       const int64_t y = side ? r1 - K + r : r0 + r;
-      const uint64_t v = cur[(y - row_base) * ws + w];
+      const uint64_t v = GOL_SCHK((cur - rsmem) + (y - row_base) * ws + w, 1, rp.smem_words) ? cur[(y - row_base) * ws + w] : 0;
       const int kind = side ? dn_kind : up_kind;
       if (kind == kRing) {
         ll_store(st->peer_ll[side][par] + (r * stride + w) * 2, v, seq);
       } else if (kind == kCluster) {
         // the neighbour's landing zone for its opposite side, same offset inside its shared memory
-        const uint32_t mine = smem_addr(land + ((1 - side) * 2 + par) * land_slot + (r * ws + w) * 2);
-        st_cluster_ll(cluster_map(mine, (uint32_t)(side ? cr + 1 : cr - 1)), v, seq);
+        const int64_t loff = (land - rsmem) + ((1 - side) * 2 + par) * land_slot + (r * ws + w) * 2;
+        const uint32_t mine = smem_addr(rsmem + loff);
+        // same layout in every CTA of the cluster: the offset is valid there iff it is valid here
+        if (GOL_SCHK(loff, 2, rp.smem_words) && (uint32_t)(side ? cr + 1 : cr - 1) < (uint32_t)cs)
+          st_cluster_ll(cluster_map(mine, (uint32_t)(side ? cr + 1 : cr - 1)), v, seq);
       } else {
         ll_store(mail_slot(rp, sidx, side ? cta + 1 : cta - 1, 1 - side, par) + (r * ws + w) * 2, v, seq);
       }
@@ -1272,7 +1291,7 @@ __global__ void __launch_bounds__(512, 1) life_resident_kernel(SlabState* states
       else if (kind == kCluster) v = poll_word(st, true, land + (side * 2 + par) * land_slot, r * ws + w, seq, side);
       else v = poll_word(st, false, mail_slot(rp, sidx, cta, side, par), r * ws + w, seq, side);
       const int64_t y = side ? r1 + r : r0 - K + r;
-      curw[(y - row_base) * ws + w] = v;
+      if (GOL_SCHK((curw - rsmem) + (y - row_base) * ws + w, 1, rp.smem_words)) curw[(y - row_base) * ws + w] = v;
     }
     __syncthreads();
     if (tid == 0) wait_acc += globaltimer_ns() - tw0;   // push is done, everything from here to the barrier is waiting
@@ -1280,7 +1299,7 @@ __global__ void __launch_bounds__(512, 1) life_resident_kernel(SlabState* states
     // ---- kk generations on a shrinking window: after generation g rows [r0-(kk-1-g), r1+(kk-1-g)) are valid
     for (int g = 0; g < kk; ++g) {
       const int m = kk - 1 - g;
-      sweep(rsmem, boff[cb], boff[cb ^ 1], K - m, K + nr + m, ws, warp, nwarps, lane);
+      sweep(rsmem, boff[cb], boff[cb ^ 1], K - m, K + nr + m, ws, warp, nwarps, lane, rp.smem_words);
       __syncthreads();
       cb ^= 1;
     }

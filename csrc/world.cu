@@ -1657,6 +1657,7 @@ static int step_cuda(gol_world* w, int64_t gens, bool launch = true) {
       rp.cluster = pl.regs_hint;
       rp.rows_alloc = pl.strip_rows + 2 * K;
       rp.use_bulk = (w->stride == w->ws) && !getenv("GOL_RESIDENT_NO_BULK");
+      rp.smem_words = (int)(resident_smem_bytes(rp.rows_alloc, w->ws, K) / 8);
       rp.mail = g.d_mail;
       rp.mail_slot = 2 * (int64_t)K * w->ws;
       rp.ctl = g.d_barrier;
