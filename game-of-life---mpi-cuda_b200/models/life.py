@@ -170,6 +170,17 @@ class Life:
     def cell_updates(self, iterations: int) -> int:
         return self.nranks * self.rows * self.width * iterations  # gol-main.c:124-125
 
+    def metrics(self, ms: float, iterations: int) -> dict:
+        """GCUPS of a step of ``iterations`` generations that took ``ms`` (whole ring), with the
+        per-GPU fraction of the bit-packed HBM roofline at this plan's generations per pass."""
+        from ..utils.metrics import gcups, roofline_fraction
+
+        total = gcups(self.cell_updates(iterations), ms * 1e-3)
+        k = max(1, int(self.plan.get("temporal_k", 1)))
+        roof = roofline_fraction(total * 1e9 / max(1, self.nranks), generations_per_pass=k)
+        return {"gcups": total, "ms": ms, "generations": iterations, "mode": self.plan["mode_name"], "k": k,
+                "hbm_roofline_fraction": roof["fraction"], "hbm_roofline_of": roof["of"]}
+
     # --------------------------------------------------------------------- io
     def dump(self, directory: Optional[str] = None) -> List[str]:
         """Write ``Rank_<r>_of_<R>.txt`` for every local slab (gol-main.c:135-139)."""

@@ -1,27 +1,8 @@
-"""Device timing with CUDA events on the launching stream (never wall clock)."""
+"""L2 flush between timed steps (device timing itself is done with CUDA events in the core:
+``World.step_timed``)."""
 from __future__ import annotations
 
 import torch
-
-
-class CudaTimer:
-    """``with CudaTimer() as t: ...`` then ``t.ms`` (synchronises on both sides)."""
-
-    def __init__(self, stream=None):
-        self.stream = stream
-        self.ms = 0.0
-
-    def __enter__(self):
-        self._a = torch.cuda.Event(enable_timing=True)
-        self._b = torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        self._a.record(self.stream)
-        return self
-
-    def __exit__(self, *exc):
-        self._b.record(self.stream)
-        torch.cuda.synchronize()
-        self.ms = self._a.elapsed_time(self._b)
 
 
 _flush_buf = {}

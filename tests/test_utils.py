@@ -31,3 +31,13 @@ def test_package_surface():
         assert hasattr(gol_b200, name)
     assert gol_b200._native.MODES == {"auto": 0, "generic": 1, "fused": 2, "persistent": 3, "tma": 4, "resident": 5}
     assert gol_b200.launch_count() >= 0
+
+
+def test_life_metrics_on_the_cpu_backend():
+    from gol_b200 import Life
+
+    life = Life(64, 32, ranks=2, backend="cpu").init(5)
+    ms = life.step_timed(8)
+    m = life.metrics(ms, 8)
+    assert m["gcups"] > 0 and m["generations"] == 8 and 0 < m["hbm_roofline_fraction"] < 1
+    life.close()
