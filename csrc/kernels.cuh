@@ -13,6 +13,8 @@ namespace gol {
 //   life_generic       N-K2  one thread per word, any shape, 1 generation, same protocol
 //   life_flow<K>       N-K3  whole step() in one launch: persistent warps pull (pass, strip) tickets and
 //                            wait on per-strip progress counters instead of a grid barrier
+//   life_resident      N-K3b whole step() with every CTA's strip resident in shared memory (small slabs):
+//                            cp.async.bulk strip load / store, halo rows over DSMEM inside clusters
 //   pattern_init       N-K4  patterns 0..6 straight into packed words
 //   halo_prime         N-K5  push my edge rows into the neighbours' recv buffers
 //   format_rows        N-K6  bits -> "0 1 0 ..." text rows on the device
